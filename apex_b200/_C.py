@@ -1,0 +1,240 @@
+"""apex_b200._C -- ctypes binding of libapex_b200.so (the C ABI in include/apex_b200.h).
+
+This module is the only place the python host code touches native code.  Every
+function below forwards to exactly one ``extern "C"`` entry point, converts a
+non-zero return code into ``RuntimeError`` and never falls back to anything
+else: if the shared library is missing the import fails with instructions to
+build it (``python -c "import __graft_entry__ as g; g.build()"``).
+
+The reference has no native layer; its intended seam is the commented-out
+``from apex_C import scale_check_overflow`` at apex/amp/scaler.py:3.
+"""
+import ctypes
+import os
+
+import torch  # noqa: F401  (loads libcudart.so.12 into the process before our library binds to it)
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "lib", "libapex_b200.so")
+
+TF_GRAD_F32 = 1
+TF_FIRST_STEP = 2
+TF_NO_MODEL = 4
+TF_UNALIGNED = 8
+TF_NO_SCALE = 16
+
+FLAG_CLEAN = 0
+INT32_MAX = 0x7FFFFFFF
+
+DTYPE_CODE = {torch.float16: 0, torch.float32: 1, torch.float64: 2}
+
+
+class MtTableStruct(ctypes.Structure):
+    _fields_ = [("d_table", ctypes.c_void_p),
+                ("n_tensors", ctypes.c_int32),
+                ("n_lists", ctypes.c_int32),
+                ("chunk_elems", ctypes.c_int32),
+                ("total_chunks", ctypes.c_int32)]
+
+
+class SgdArgs(ctypes.Structure):
+    _fields_ = [("lr", ctypes.c_double), ("momentum", ctypes.c_double),
+                ("dampening", ctypes.c_double), ("weight_decay", ctypes.c_double),
+                ("nesterov", ctypes.c_int32), ("apply_scale", ctypes.c_int32),
+                ("inv_scale", ctypes.c_double)]
+
+
+class AdamArgs(ctypes.Structure):
+    _fields_ = [("lr", ctypes.c_double), ("beta1", ctypes.c_double), ("beta2", ctypes.c_double),
+                ("eps", ctypes.c_double), ("weight_decay", ctypes.c_double),
+                ("step_size", ctypes.c_double), ("bias_correction2_sqrt", ctypes.c_double),
+                ("decoupled_weight_decay", ctypes.c_int32), ("apply_scale", ctypes.c_int32),
+                ("inv_scale", ctypes.c_double)]
+
+
+_vp = ctypes.c_void_p
+_i = ctypes.c_int
+_d = ctypes.c_double
+_tp = ctypes.POINTER(MtTableStruct)
+
+# name -> (restype, argtypes); mirrors include/apex_b200.h one to one.
+SIGNATURES = {
+    "apex_b200_version": (_i, []),
+    "apex_b200_error_string": (ctypes.c_char_p, [_i]),
+    "apex_b200_device_info": (_i, [ctypes.POINTER(_i)] * 3),
+    "apex_b200_mt_table_bytes": (ctypes.c_size_t, [_i, _i]),
+    "apex_b200_mt_table_pack": (_i, [_vp, ctypes.c_size_t, _i, _i, _vp, _vp, _vp, _i, _tp]),
+    "apex_b200_flag_clear": (_i, [_vp, _vp]),
+    "apex_b200_mt_check_overflow": (_i, [_tp, _i, _vp, _vp]),
+    "apex_b200_mt_unscale": (_i, [_tp, _i, _d, _vp, _i, _vp]),
+    "apex_b200_mt_grads_to_master": (_i, [_tp, _i, _i, _d, _i, _vp, _vp]),
+    "apex_b200_mt_master_to_model": (_i, [_tp, _i, _i, _vp, _vp]),
+    "apex_b200_mt_copy": (_i, [_tp, _i, _i, _i, _vp, _vp]),
+    "apex_b200_mt_zero": (_i, [_tp, _i, _i, _vp]),
+    "apex_b200_mt_fused_sgd": (_i, [_tp, ctypes.POINTER(SgdArgs), _vp, _vp]),
+    "apex_b200_mt_fused_adam": (_i, [_tp, ctypes.POINTER(AdamArgs), _vp, _vp]),
+    "apex_b200_mt_flatten": (_i, [_tp, _i, _vp, _i, _vp]),
+    "apex_b200_mt_scale_unflatten": (_i, [_tp, _vp, _i, _i, _d, _i, _vp, _vp]),
+    "apex_b200_scale_flat": (_i, [_vp, ctypes.c_int64, _i, _d, _vp, _vp]),
+    "apex_b200_mt_l2norm": (_i, [_tp, _i, _d, _i, _vp, ctypes.c_int64, _vp, _vp]),
+    "apex_b200_mt_clip_by_norm": (_i, [_tp, _i, _vp, _d, _vp, _vp]),
+}
+
+
+def _load():
+    if not os.path.exists(LIB_PATH):
+        raise ImportError(
+            "apex_b200: native library not built (%s missing). There is no python or CPU "
+            "fallback for this path; build it with `make -C apex_b200/csrc` or "
+            "`python -c \"import __graft_entry__ as g; g.build()\"`." % LIB_PATH)
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)   # AttributeError here = header and library out of sync
+        fn.restype = res
+        fn.argtypes = args
+    return lib
+
+
+lib = _load()
+
+# Launch counter: bench.py reports how many of OUR kernels ran in the timed region.
+launches = 0
+
+
+def error_string(code):
+    return lib.apex_b200_error_string(int(code)).decode()
+
+
+def _check(code, what):
+    if code != 0:
+        raise RuntimeError("%s failed: %s (code %d)" % (what, error_string(code), code))
+
+
+def version():
+    return lib.apex_b200_version()
+
+
+def device_info():
+    sm, ma, mi = _i(), _i(), _i()
+    _check(lib.apex_b200_device_info(ctypes.byref(sm), ctypes.byref(ma), ctypes.byref(mi)), "device_info")
+    return sm.value, ma.value, mi.value
+
+
+def current_stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def table_bytes(n_tensors, n_lists):
+    return lib.apex_b200_mt_table_bytes(n_tensors, n_lists)
+
+
+def table_pack(host_ptr, host_bytes, n_tensors, n_lists, numels_ptr, ptrs_ptr, flags_ptr, chunk_elems):
+    out = MtTableStruct()
+    _check(lib.apex_b200_mt_table_pack(host_ptr, host_bytes, n_tensors, n_lists, numels_ptr, ptrs_ptr,
+                                       flags_ptr, chunk_elems, ctypes.byref(out)), "mt_table_pack")
+    return out
+
+
+def flag_clear(flag, stream=None):
+    _check(lib.apex_b200_flag_clear(_ptr(flag), current_stream() if stream is None else stream), "flag_clear")
+
+
+def _count(table):
+    global launches
+    if table.struct.total_chunks > 0:
+        launches += 1
+
+
+def mt_check_overflow(table, grad_list, flag, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_check_overflow(table.ref, grad_list, _ptr(flag),
+                                           current_stream() if stream is None else stream), "mt_check_overflow")
+
+
+def mt_unscale(table, grad_list, inv_scale, flag, mode, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_unscale(table.ref, grad_list, float(inv_scale), _ptr(flag), mode,
+                                    current_stream() if stream is None else stream), "mt_unscale")
+
+
+def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_grads_to_master(table.ref, src_list, dst_list, float(inv_scale), int(apply_scale),
+                                            _ptr(flag), current_stream() if stream is None else stream),
+           "mt_grads_to_master")
+
+
+def mt_master_to_model(table, src_list, dst_list, flag, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_master_to_model(table.ref, src_list, dst_list, _ptr(flag),
+                                            current_stream() if stream is None else stream), "mt_master_to_model")
+
+
+def mt_copy(table, src_list, dst_list, elem_size, flag, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_copy(table.ref, src_list, dst_list, elem_size, _ptr(flag),
+                                 current_stream() if stream is None else stream), "mt_copy")
+
+
+def mt_zero(table, lst, elem_size, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_zero(table.ref, lst, elem_size, current_stream() if stream is None else stream),
+           "mt_zero")
+
+
+def mt_fused_sgd(table, lr, momentum, dampening, weight_decay, nesterov, inv_scale, apply_scale, flag,
+                 stream=None):
+    _count(table)
+    a = SgdArgs(float(lr), float(momentum), float(dampening), float(weight_decay), int(bool(nesterov)),
+                int(bool(apply_scale)), float(inv_scale))
+    _check(lib.apex_b200_mt_fused_sgd(table.ref, ctypes.byref(a), _ptr(flag),
+                                      current_stream() if stream is None else stream), "mt_fused_sgd")
+
+
+def mt_fused_adam(table, lr, beta1, beta2, eps, weight_decay, step_size, bias_correction2_sqrt,
+                  decoupled_weight_decay, inv_scale, apply_scale, flag, stream=None):
+    _count(table)
+    a = AdamArgs(float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(step_size),
+                 float(bias_correction2_sqrt), int(bool(decoupled_weight_decay)), int(bool(apply_scale)),
+                 float(inv_scale))
+    _check(lib.apex_b200_mt_fused_adam(table.ref, ctypes.byref(a), _ptr(flag),
+                                       current_stream() if stream is None else stream), "mt_fused_adam")
+
+
+def mt_flatten(table, src_list, flat, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_flatten(table.ref, src_list, _ptr(flat), flat.element_size(),
+                                    current_stream() if stream is None else stream), "mt_flatten")
+
+
+def mt_scale_unflatten(table, flat, dst_list, divisor, apply_mul, flag, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_scale_unflatten(table.ref, _ptr(flat), dst_list, DTYPE_CODE[flat.dtype],
+                                            float(divisor), int(bool(apply_mul)), _ptr(flag),
+                                            current_stream() if stream is None else stream), "mt_scale_unflatten")
+
+
+def scale_flat(flat, divisor, flag, stream=None):
+    global launches
+    if flat.numel() > 0:
+        launches += 1
+    _check(lib.apex_b200_scale_flat(_ptr(flat), flat.numel(), DTYPE_CODE[flat.dtype], float(divisor), _ptr(flag),
+                                    current_stream() if stream is None else stream), "scale_flat")
+
+
+def mt_l2norm(table, grad_list, inv_scale, apply_scale, partials, norm_out, stream=None):
+    global launches
+    launches += 2 if table.struct.total_chunks > 0 else 1
+    _check(lib.apex_b200_mt_l2norm(table.ref, grad_list, float(inv_scale), int(bool(apply_scale)), _ptr(partials),
+                                   0 if partials is None else partials.numel(), _ptr(norm_out),
+                                   current_stream() if stream is None else stream), "mt_l2norm")
+
+
+def mt_clip_by_norm(table, grad_list, norm, max_norm, flag, stream=None):
+    _count(table)
+    _check(lib.apex_b200_mt_clip_by_norm(table.ref, grad_list, _ptr(norm), float(max_norm), _ptr(flag),
+                                         current_stream() if stream is None else stream), "mt_clip_by_norm")

@@ -1,0 +1,14 @@
+"""Same export list as the reference's apex/fp16_utils/__init__.py:1-19."""
+from .fp16util import (
+    BN_convert_float,
+    network_to_half,
+    prep_param_lists,
+    model_grads_to_master_grads,
+    master_params_to_model_params,
+    tofp16,
+    to_python_float,
+    clip_grad_norm,
+)
+from .fused_weight_norm import Fused_Weight_Norm
+from .fp16_optimizer import FP16_Optimizer
+from .loss_scaler import LossScaler, DynamicLossScaler

@@ -1,0 +1,671 @@
+"""FP16_Optimizer on B200 kernels (reference: apex/fp16_utils/fp16_optimizer.py).
+
+Public surface, attribute names, messages and return values are the
+reference's.  What is different is what runs on the GPU:
+
+reference, per iteration (fp16_optimizer.py:486-497, :330-384)
+    has_overflow      2 launches + 1 blocking D2H read PER TENSOR   (loss_scaler.py:84-110)
+    grads -> masters  1 copy_ per tensor                             (fp16util.py:106-112)
+    downscale         1 mul_ per tensor                              (:236-241)
+    optimizer.step()  torch foreach, 3-5 passes over every array     (:380)
+    masters -> model  1 copy_ per tensor                             (fp16util.py:127-129)
+
+here
+    update_master_grads   ONE check launch over all gradients -> one device word,
+                          copied to pinned host memory asynchronously.  The fp16
+                          gradients are NOT expanded to fp32 yet: the master
+                          gradients stay "virtual" (= float(g16) * 1/scale).
+    step                  ONE fused launch per param group: unscale -> update of
+                          master + state -> fp16 model copy, predicated on the
+                          device word (a skipped step touches nothing).  Only
+                          then does the host wait for the word, to drive
+                          update_scale / the OVERFLOW message exactly as the
+                          reference does.
+
+Anything that looks at a master gradient in between (``clip_master_grads``, an
+inner optimizer other than SGD/Adam/AdamW, a closure, user code reading
+``master.grad``) makes the virtual gradients real first -- masters are a Tensor
+subclass whose ``grad`` property does that -- and from there on the code follows
+the reference's unfused sequence on multi-tensor kernels.  DESIGN.md lists the
+(few, deliberate) observable differences.
+"""
+import weakref
+
+import torch
+
+from .. import _C
+from ..multi_tensor import TensorTable, CHUNK_STEP, CHUNK_STREAM, new_flag
+from .loss_scaler import DynamicLossScaler, LossScaler
+from .fp16util import master_params_to_model_params, clip_grad_norm
+
+_tensor_grad = torch._C.TensorBase.grad
+
+
+class _MasterParam(torch.Tensor):
+    """fp32 master copy of an fp16 parameter.
+
+    Behaves like the plain fp32 leaf tensor the reference creates
+    (fp16_optimizer.py:135-136).  Reading ``.grad`` first asks the owning
+    FP16_Optimizer to materialise pending master gradients.
+    """
+    __torch_function__ = torch._C._disabled_torch_function_impl
+
+    @property
+    def grad(self):
+        owner = self.__dict__.get("_apex_owner")
+        if owner is not None:
+            owner = owner()
+            if owner is not None and owner._pending is not None:
+                owner._materialize_master_grads()
+        return _tensor_grad.__get__(self)
+
+    @grad.setter
+    def grad(self, value):
+        _tensor_grad.__set__(self, value)
+
+    @grad.deleter
+    def grad(self):
+        _tensor_grad.__delete__(self)
+
+    def __reduce_ex__(self, proto):
+        # checkpoints hold plain fp32 tensors, exactly what the reference saves
+        # under 'fp32_from_fp16' (fp16_optimizer.py:284)
+        plain = self.detach().requires_grad_(self.requires_grad)
+        return plain.__reduce_ex__(proto)
+
+
+def _raw_grad(t):
+    """``t.grad`` without triggering materialisation."""
+    return _tensor_grad.__get__(t)
+
+
+class FP16_Optimizer(object):
+    """Wraps ``init_optimizer`` and manages fp32 master weights and loss scaling.
+
+    Same constructor and methods as the reference class
+    (fp16_optimizer.py:11-551); see the module docstring for what runs where.
+    """
+
+    def __init__(self,
+                 init_optimizer,
+                 static_loss_scale=1.0,
+                 dynamic_loss_scale=False,
+                 dynamic_loss_args=None,
+                 verbose=True):
+        self.verbose = verbose
+        self.optimizer = init_optimizer
+
+        self.fp16_groups = []
+        self.fp32_from_fp16_groups = []
+        self.fp32_from_fp32_groups = []
+        self._pending = None          # (inv_scale, apply_scale): master grads are float(g16)*inv_scale, not stored
+        self._grads_ready = False     # master grads are materialised and current
+        self_ref = weakref.ref(self)
+        for gi, param_group in enumerate(self.optimizer.param_groups):
+            self.maybe_print("FP16_Optimizer processing param group {}:".format(gi))
+            halves, masters, floats = [], [], []
+            for pi, param in enumerate(param_group['params']):
+                if not param.requires_grad:
+                    continue
+                kind = param.type()
+                if kind == 'torch.cuda.HalfTensor':
+                    self.maybe_print("FP16_Optimizer received torch.cuda.HalfTensor with {}"
+                                     .format(param.size()))
+                    halves.append(param)
+                    master = param.detach().clone().float().as_subclass(_MasterParam)
+                    master.requires_grad = True
+                    master.__dict__["_apex_owner"] = self_ref
+                    param_group['params'][pi] = master
+                    masters.append(master)
+                    # keep any state the wrapped optimizer already had for this param
+                    if param in self.optimizer.state:
+                        self.optimizer.state[master] = self.optimizer.state.pop(param)
+                elif kind == 'torch.cuda.FloatTensor':
+                    self.maybe_print("FP16_Optimizer received torch.cuda.FloatTensor with {}"
+                                     .format(param.size()))
+                    floats.append(param)
+                    param_group['params'][pi] = param
+                else:
+                    raise TypeError("Wrapped parameters must be either "
+                                    "torch.cuda.FloatTensor or torch.cuda.HalfTensor. "
+                                    "Received {}".format(kind))
+            self.fp16_groups.append(halves)
+            self.fp32_from_fp16_groups.append(masters)
+            self.fp32_from_fp32_groups.append(floats)
+
+        # recast pre-existing per-param state to the masters' dtype (reference :158)
+        self.optimizer.load_state_dict(self.optimizer.state_dict())
+
+        if dynamic_loss_scale:
+            self.dynamic_loss_scale = True
+            if dynamic_loss_args is not None:
+                self.loss_scaler = DynamicLossScaler(**dynamic_loss_args)
+            else:
+                self.loss_scaler = DynamicLossScaler()
+        else:
+            self.dynamic_loss_scale = False
+            self.loss_scaler = LossScaler(static_loss_scale)
+
+        self._overflow = False
+        self._overflow_event = None      # set while the device word has not been read yet
+        self.first_closure_call_this_step = True
+        self.clip_grad_norm = clip_grad_norm
+
+        # device-side plumbing (created on first use)
+        self._device = None
+        self._flag = None                # the single overflow word
+        self._flag_host = None           # its pinned host mirror
+        self._check_table = None         # all gradients, for the overflow scan
+        self._unscale_table = None       # fp32-native gradients, unscaled in place
+        self._grad_tables = {}           # group index -> table for materialisation
+        self._step_tables = {}           # group index -> table for the fused step
+        self._zero_table = None
+        self._norm_buf = None
+
+    # ---- small helpers -------------------------------------------------------
+
+    def maybe_print(self, msg):
+        if self.verbose:
+            print(msg)
+
+    def __getstate__(self):
+        raise RuntimeError("FP16_Optimizer should be serialized using state_dict().")
+
+    def __setstate__(self, state):
+        raise RuntimeError("FP16_Optimizer should be deserialized using load_state_dict().")
+
+    def _ensure_device(self, tensor):
+        if self._device is None:
+            self._device = tensor.device
+            self._flag = new_flag(self._device)
+            self._flag_host = torch.zeros(1, dtype=torch.int32,
+                                          pin_memory=(self._device.type == "cuda"))
+
+    # ``overflow`` is a plain bool in the reference.  Here the truth may still
+    # be on the device; reading the attribute waits for it (once).
+    def _get_overflow(self):
+        ev = self._overflow_event
+        if ev is not None:
+            ev.synchronize()
+            self._overflow = int(self._flag_host[0]) != 0
+            self._overflow_event = None
+        return self._overflow
+
+    def _set_overflow(self, value):
+        self._overflow_event = None
+        self._overflow = value
+
+    overflow = property(_get_overflow, _set_overflow)
+
+    def _live_flag(self):
+        """Device word that predicates kernels, or None when no check is pending/needed."""
+        return self._flag if self._overflow_event is not None else None
+
+    # ---- zero_grad -------------------------------------------------------------
+
+    def zero_grad(self, set_grads_to_None=False):
+        """Zero (or drop) fp32 and fp16 gradients (reference: :187-211), in one launch."""
+        self._pending = None
+        self._grads_ready = False
+        if set_grads_to_None:
+            for group in self.optimizer.param_groups:
+                for p in group['params']:
+                    p.grad = None
+            for fp16_group in self.fp16_groups:
+                for param in fp16_group:
+                    param.grad = None
+            return
+        grads = []
+        for group in self.optimizer.param_groups:
+            for p in group['params']:
+                g = _raw_grad(p)
+                if g is not None:
+                    g.detach_()
+                    grads.append(g)
+        for fp16_group in self.fp16_groups:
+            for param in fp16_group:
+                if param.grad is not None:
+                    param.grad.detach_()
+                    grads.append(param.grad)
+        if not grads:
+            return
+        flags = []
+        for g in grads:
+            if g.dtype == torch.float32:
+                flags.append(_C.TF_GRAD_F32)
+            elif g.dtype == torch.float16:
+                flags.append(0)
+            else:
+                raise TypeError("apex_b200: unexpected gradient dtype %s" % g.dtype)
+        self._ensure_device(grads[0])
+        if self._zero_table is None:
+            self._zero_table = TensorTable(self._device, 1, CHUNK_STREAM)
+        self._zero_table.update([grads], flags)
+        _C.mt_zero(self._zero_table, 0, 2)
+
+    # ---- overflow check ----------------------------------------------------------
+
+    def _check_overflow(self):
+        """Scan fp16 grads then fp32-native grads (reference order, :213-221); no host sync."""
+        grads, flags = [], []
+        for group in self.fp16_groups:
+            for param in group:
+                if param.grad is not None:
+                    grads.append(param.grad.data)
+                    flags.append(0)
+        for group in self.fp32_from_fp32_groups:
+            for param in group:
+                if param.grad is not None:
+                    grads.append(param.grad.data)
+                    flags.append(_C.TF_GRAD_F32)
+        if not isinstance(self.loss_scaler, DynamicLossScaler):
+            # a user-supplied scaler object: ask it, as the reference does
+            params = [p for g in self.fp16_groups for p in g] + \
+                     [p for g in self.fp32_from_fp32_groups for p in g]
+            self.overflow = self.loss_scaler.has_overflow(params)
+            return
+        if not grads:
+            self.overflow = False
+            return
+        self._ensure_device(grads[0])
+        if self._check_table is None:
+            self._check_table = TensorTable(self._device, 1, CHUNK_STREAM)
+        for g in grads:
+            if not g.is_contiguous():
+                raise RuntimeError("apex_b200: gradients must be contiguous")
+        self._check_table.update([grads], flags)
+        _C.flag_clear(self._flag)
+        _C.mt_check_overflow(self._check_table, 0, self._flag)
+        self._flag_host.copy_(self._flag, non_blocking=True)
+        ev = torch.cuda.Event()
+        ev.record()
+        self._overflow_event = ev
+
+    def _update_scale(self, has_overflow=False):
+        self.loss_scaler.update_scale(has_overflow)
+
+    # ---- master <-> model ------------------------------------------------------------
+
+    def _master_params_to_model_params(self):
+        for fp16_group, fp32_from_fp16_group in zip(self.fp16_groups, self.fp32_from_fp16_groups):
+            if fp16_group:
+                master_params_to_model_params(fp16_group, fp32_from_fp16_group)
+
+    def _materialize_master_grads(self):
+        """Make the virtual master gradients real: the reference's
+        ``_model_grads_to_master_grads`` + ``_downscale_master`` for the masters
+        (:232-241), including its early return on overflow (:493-495)."""
+        pending, self._pending = self._pending, None
+        if pending is None:
+            return
+        inv_scale, apply_scale = pending
+        if self.overflow:      # waits for the device word; master grads stay as they were
+            return
+        self._grads_ready = True
+        for gi, (fp16_group, masters) in enumerate(zip(self.fp16_groups, self.fp32_from_fp16_groups)):
+            srcs, dsts = [], []
+            for model, master in zip(fp16_group, masters):
+                if model.grad is not None:
+                    mg = _raw_grad(master)
+                    if mg is None:
+                        mg = torch.empty_like(master.data)
+                        master.grad = mg
+                    srcs.append(model.grad.data)
+                    dsts.append(mg.data)
+                else:
+                    master.grad = None
+            if not srcs:
+                continue
+            table = self._grad_tables.get(gi)
+            if table is None:
+                table = self._grad_tables[gi] = TensorTable(self._device, 2, CHUNK_STREAM)
+            table.update([srcs, dsts])
+            _C.mt_grads_to_master(table, 0, 1, inv_scale, apply_scale, None)
+
+    def _model_grads_to_master_grads(self):
+        # kept for API parity with the reference (:232-234); scale 1 = plain copy
+        self._pending = (1.0, False)
+        self._materialize_master_grads()
+
+    def _downscale_master(self):
+        """In-place unscale of every fp32 gradient the inner optimizer owns (reference :236-241)."""
+        if self.loss_scale != 1.0:
+            grads = []
+            for group in self.optimizer.param_groups:
+                for param in group['params']:
+                    if param.grad is not None:
+                        grads.append(param.grad.data)
+            self._unscale_in_place(grads, 1. / self.loss_scale, None)
+
+    def _unscale_in_place(self, grads, inv_scale, flag):
+        if not grads:
+            return
+        self._ensure_device(grads[0])
+        if self._unscale_table is None:
+            self._unscale_table = TensorTable(self._device, 1, CHUNK_STREAM)
+        self._unscale_table.update([grads], [_C.TF_GRAD_F32] * len(grads))
+        _C.mt_unscale(self._unscale_table, 0, inv_scale, flag, 0)
+
+    # ---- clip ---------------------------------------------------------------------------
+
+    def clip_master_grads(self, max_norm, norm_type=2):
+        """Clip the fp32 master gradients (reference: :243-265).
+
+        Returns the total norm, or -1 if the last gradients overflowed.
+        """
+        if not self.overflow:
+            fp32_params = []
+            for param_group in self.optimizer.param_groups:
+                for param in param_group['params']:
+                    fp32_params.append(param)
+            return self.clip_grad_norm(fp32_params, max_norm, norm_type)
+        else:
+            return -1
+
+    # ---- checkpointing --------------------------------------------------------------------
+
+    def state_dict(self):
+        """Same keys as the reference (:267-286)."""
+        state_dict = {}
+        state_dict['loss_scaler'] = self.loss_scaler
+        state_dict['dynamic_loss_scale'] = self.dynamic_loss_scale
+        state_dict['overflow'] = self.overflow
+        state_dict['first_closure_call_this_step'] = self.first_closure_call_this_step
+        state_dict['optimizer_state_dict'] = self.optimizer.state_dict()
+        state_dict['fp32_from_fp16'] = self.fp32_from_fp16_groups
+        return state_dict
+
+    def load_state_dict(self, state_dict):
+        """Restore scaler, flags, inner optimizer and the saved fp32 masters (reference: :288-328)."""
+        self._pending = None
+        self._grads_ready = False
+        self.loss_scaler = state_dict['loss_scaler']
+        self.dynamic_loss_scale = state_dict['dynamic_loss_scale']
+        self.overflow = state_dict['overflow']
+        self.first_closure_call_this_step = state_dict['first_closure_call_this_step']
+        self.optimizer.load_state_dict(state_dict['optimizer_state_dict'])
+        for current_group, saved_group in zip(self.fp32_from_fp16_groups, state_dict['fp32_from_fp16']):
+            for current, saved in zip(current_group, saved_group):
+                current.data.copy_(saved.data)
+        for t in self._step_tables.values():
+            t.invalidate()
+
+    # ---- step -----------------------------------------------------------------------------------
+
+    def step(self, closure=None):
+        """Update masters with the wrapped optimizer's rule, refresh the fp16 params
+        (reference: :330-384).  On overflow: adjust the scale, print, skip."""
+        scale = self.loss_scaler.loss_scale
+
+        # Launch the (device-predicated) fused update before the host looks at
+        # the overflow word, so the GPU never waits for the host.
+        commit = None
+        if closure is None:
+            commit = self._launch_fused_step()
+
+        overflow = self.overflow
+        self._update_scale(overflow)
+
+        if overflow:
+            print("OVERFLOW! Skipping step. Attempted loss scale: {}, reducing to {}"
+                  .format(scale, self.loss_scale))
+            return
+
+        if closure is not None:
+            retval = self._step_with_closure(closure)
+            self._master_params_to_model_params()
+        elif commit is not None:
+            commit()
+            retval = None
+        else:
+            retval = self.optimizer.step()
+            self._master_params_to_model_params()
+
+        return retval
+
+    def _step_with_closure(self, closure):
+        """reference: :386-423"""
+        def wrapped_closure():
+            if self.first_closure_call_this_step:
+                # fp16 params are fresh on entry to step()
+                self.first_closure_call_this_step = False
+            else:
+                # the inner optimizer moved the masters since the last call and
+                # knows nothing about the fp16 copies
+                self._master_params_to_model_params()
+            temp_loss = closure()
+            while self.overflow:
+                scale = self.loss_scaler.loss_scale
+                self._update_scale(self.overflow)
+                print("OVERFLOW within closure! Skipping step. Attempted loss scale: {}, "
+                      "reducing to {}".format(scale, self.loss_scale))
+                temp_loss = closure()
+            return temp_loss
+
+        retval = self.optimizer.step(wrapped_closure)
+        self.first_closure_call_this_step = True
+        return retval
+
+    # ---- the fused path ---------------------------------------------------------------------------
+
+    def _fused_kind(self):
+        opt = self.optimizer
+        if type(opt) is torch.optim.SGD:
+            return "sgd"
+        if type(opt) is torch.optim.Adam or type(opt) is torch.optim.AdamW:
+            return "adam"
+        return None
+
+    def _launch_fused_step(self):
+        """Enqueue one fused launch per param group if every precondition holds.
+
+        Returns a ``commit`` callable (to run once the step is known not to be
+        skipped: it publishes new optimizer state such as momentum buffers and
+        Adam's step count), or None when the generic path must be taken.
+        Nothing is launched in that case.
+        """
+        pending = self._pending
+        kind = self._fused_kind()
+        if kind is None or (pending is None and not self._grads_ready):
+            return None
+        if self._overflow_event is None and self._overflow:
+            return None           # overflow already known on the host: step() skips
+        from_masters = pending is None     # gradients were materialised (e.g. for clipping)
+        inv_scale, apply_scale = (1.0, False) if from_masters else pending
+        plans = []
+        for gi, group in enumerate(self.optimizer.param_groups):
+            plan = self._plan_group(kind, gi, group, from_masters)
+            if plan is False:
+                return None
+            if plan is not None:
+                plans.append(plan)
+        flag = self._live_flag()
+        commits = []
+        for gi, group, lists, flags, extra in plans:
+            table = self._step_tables.get(gi)
+            if table is None or table.n_lists != len(lists):
+                table = self._step_tables[gi] = TensorTable(self._device, len(lists), CHUNK_STEP)
+            table.update(lists, flags)
+            if kind == "sgd":
+                _C.mt_fused_sgd(table, group['lr'], group['momentum'], group['dampening'],
+                                group['weight_decay'], group['nesterov'], inv_scale, apply_scale, flag)
+            else:
+                _C.mt_fused_adam(table, group['lr'], group['betas'][0], group['betas'][1], group['eps'],
+                                 group['weight_decay'], extra['step_size'], extra['bc2_sqrt'],
+                                 extra['decoupled'], inv_scale, apply_scale, flag)
+            commits.append(extra['commit'])
+
+        def commit():
+            for c in commits:
+                c()
+        return commit
+
+    def _plan_group(self, kind, gi, group, from_masters):
+        """Tensor lists for one param group; False = not fusable, None = nothing to do."""
+        if group.get('maximize', False) or group.get('differentiable', False):
+            return False
+        if isinstance(group['lr'], torch.Tensor):
+            return False
+        halves = self.fp16_groups[gi]
+        masters = self.fp32_from_fp16_groups[gi]
+        floats = self.fp32_from_fp32_groups[gi]
+        if len(halves) + len(floats) != len(group['params']):
+            return False          # param_groups edited behind our back
+        grads, params, models, flags = [], [], [], []
+        for model, master in zip(halves, masters):
+            if from_masters:
+                g, want, fl = _raw_grad(master), torch.float32, _C.TF_GRAD_F32 | _C.TF_NO_SCALE
+            else:
+                g, want, fl = model.grad, torch.float16, 0
+            if g is None or g.dtype != want or g.is_sparse or not g.is_contiguous():
+                return False
+            grads.append(g.data)
+            params.append(master.data)
+            models.append(model.data)
+            flags.append(fl)
+        for p in floats:
+            g = p.grad
+            if g is None or g.dtype != torch.float32 or g.is_sparse or not g.is_contiguous():
+                return False
+            grads.append(g.data)
+            params.append(p.data)
+            models.append(None)
+            # already unscaled in place by update_master_grads, as the reference does
+            flags.append(_C.TF_GRAD_F32 | _C.TF_NO_MODEL | _C.TF_NO_SCALE)
+        if not grads:
+            return None
+        for t in params + [m for m in models if m is not None]:
+            if not t.is_contiguous():
+                return False
+        self._ensure_device(grads[0])
+        owners = masters + floats          # keys of optimizer.state
+        if kind == "sgd":
+            return self._plan_sgd(gi, group, owners, grads, params, models, flags)
+        return self._plan_adam(gi, group, owners, grads, params, models, flags)
+
+    def _plan_sgd(self, gi, group, owners, grads, params, models, flags):
+        state = self.optimizer.state
+        bufs, fresh = [], []
+        if group['momentum'] != 0:
+            for i, p in enumerate(owners):
+                buf = state[p].get('momentum_buffer') if p in state else None
+                if buf is None:
+                    # torch: buf = clone(grad) on the first step (sgd.py:361-362, :452-455)
+                    buf = torch.empty_like(params[i])
+                    fresh.append((p, buf))
+                    flags[i] |= _C.TF_FIRST_STEP
+                elif buf.dtype != torch.float32 or not buf.is_contiguous():
+                    return False
+                bufs.append(buf)
+        else:
+            bufs = [None] * len(owners)
+
+        def commit():
+            for p, buf in fresh:
+                state[p]['momentum_buffer'] = buf
+        return gi, group, [grads, params, bufs, models], flags, {'commit': commit}
+
+    def _plan_adam(self, gi, group, owners, grads, params, models, flags):
+        if group.get('amsgrad', False) or group.get('capturable', False):
+            return False
+        beta1, beta2 = group['betas']
+        if isinstance(beta1, torch.Tensor) or isinstance(beta2, torch.Tensor):
+            return False
+        state = self.optimizer.state
+        ms, vs, fresh, steps = [], [], [], []
+        for i, p in enumerate(owners):
+            st = state[p] if p in state else {}
+            if len(st) == 0:
+                # torch's lazy state init (adam.py:_init_group)
+                step_dtype = torch.float64 if torch.get_default_dtype() == torch.float64 else torch.float32
+                new = {'step': torch.tensor(0.0, dtype=step_dtype),
+                       'exp_avg': torch.zeros_like(params[i], memory_format=torch.preserve_format),
+                       'exp_avg_sq': torch.zeros_like(params[i], memory_format=torch.preserve_format)}
+                fresh.append((p, new))
+                st = new
+            if not isinstance(st['step'], torch.Tensor) or st['step'].is_cuda:
+                return False
+            m, v = st['exp_avg'], st['exp_avg_sq']
+            if m.dtype != torch.float32 or v.dtype != torch.float32 or \
+                    not m.is_contiguous() or not v.is_contiguous():
+                return False
+            ms.append(m)
+            vs.append(v)
+            steps.append(st['step'])
+        step_vals = set(float(s) for s in steps)
+        if len(step_vals) != 1:
+            return False          # per-tensor step counts differ: let torch handle it
+        step = step_vals.pop() + 1
+        # torch/optim/adam.py:764-775, in python doubles
+        bias_correction1 = 1 - beta1 ** step
+        bias_correction2 = 1 - beta2 ** step
+        step_size = (group['lr'] / bias_correction1) * -1
+        bc2_sqrt = bias_correction2 ** 0.5
+
+        def commit():
+            for p, new in fresh:
+                state[p].update(new)
+            torch._foreach_add_(steps, 1)
+        extra = {'step_size': step_size, 'bc2_sqrt': bc2_sqrt,
+                 'decoupled': bool(group.get('decoupled_weight_decay', False)), 'commit': commit}
+        return gi, group, [grads, params, ms, vs, models], flags, extra
+
+    # ---- backward ---------------------------------------------------------------------------------------
+
+    def backward(self, loss, update_master_grads=True):
+        """Scale the loss in fp32, backpropagate, then refresh the master gradients
+        (reference: :425-484)."""
+        self.loss_scaler.backward(loss.float())
+        if update_master_grads:
+            self.update_master_grads()
+
+    def update_master_grads(self):
+        """Check the fresh fp16 gradients and (virtually) copy/unscale them into the
+        masters (reference: :486-497)."""
+        self._pending = None
+        self._grads_ready = False
+        if self.dynamic_loss_scale:
+            self._check_overflow()
+            # reference: `if self.overflow: return`.  The decision is still on the
+            # device; everything enqueued below is predicated on it instead.
+        loss_scale = self.loss_scale
+        apply_scale = loss_scale != 1.0
+        inv_scale = 1. / loss_scale if apply_scale else 1.0
+        flag = self._live_flag()
+        if flag is None and self.dynamic_loss_scale and self.overflow:
+            return          # overflow already known on the host (custom scaler path)
+        # fp32-native parameters are the user's own tensors: unscale in place now.
+        if apply_scale:
+            grads = [p.grad.data for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
+            self._unscale_in_place(grads, inv_scale, flag)
+        self._pending = (inv_scale, apply_scale)
+
+    def inspect_master_grad_data(self):
+        """reference: :499-522 -- not implemented there either."""
+        raise NotImplementedError("Currently not implemented, working on it...")
+
+    # ---- promoted attributes (reference: :524-550) --------------------------------------------------------
+
+    def _get_loss_scale(self):
+        return self.loss_scaler.loss_scale
+
+    def _set_loss_scale(self, value):
+        self.loss_scaler.cur_scale = value
+
+    loss_scale = property(_get_loss_scale, _set_loss_scale)
+
+    def _get_state(self):
+        return self.optimizer.state
+
+    def _set_state(self, value):
+        self.optimizer.state = value
+
+    state = property(_get_state, _set_state)
+
+    def _get_param_groups(self):
+        return self.optimizer.param_groups
+
+    def _set_param_groups(self, value):
+        self.optimizer.param_groups = value
+
+    param_groups = property(_get_param_groups, _set_param_groups)

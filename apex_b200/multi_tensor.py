@@ -1,0 +1,98 @@
+"""Device-resident tensor tables for the multi-tensor-apply kernels.
+
+The reference walks python lists and launches one stock torch op per tensor
+(e.g. apex/fp16_utils/fp16util.py:106-112, apex/fp16_utils/fp16_optimizer.py:236-241).
+Here a list-of-lists of tensors is described once by a small table in HBM
+(layout in include/apex_b200.h) and one launch covers all of it.  The table is
+rebuilt only when a pointer, size or flag changes: callers pass the current
+tensors every time and ``update`` compares their addresses with the cached key.
+
+Ownership: torch owns every tensor; the table borrows raw addresses for the
+duration of the launches the caller enqueues right after ``update`` and never
+frees or retains them (SURVEY.md 8b "Ownership").
+"""
+import numpy as np
+import torch
+
+from . import _C
+
+# Elements per chunk.  A chunk never straddles a tensor; a CTA processes one
+# chunk at a time with 256 threads x 8 elements per step.
+CHUNK_STEP = 16384      # fused update kernels (Adam: 448 KiB of traffic per chunk)
+CHUNK_STREAM = 65536    # pure streaming kernels (check / convert / flatten / zero)
+
+
+class TensorTable(object):
+    """One packed table: ``n_lists`` parallel lists of ``n`` tensors each."""
+
+    def __init__(self, device, n_lists, chunk_elems):
+        self.device = torch.device(device)
+        self.n_lists = n_lists
+        self.chunk_elems = chunk_elems
+        self.struct = _C.MtTableStruct()
+        self.ref = None
+        self.n = 0
+        self.total_numel = 0
+        self._key = None
+        self._host = None      # pinned staging buffer
+        self._dev = None       # device copy
+        self._copied = None    # event: staging buffer free for reuse
+        self.lists = None      # kept only when _C.keep_table_refs is set (CPU test doubles)
+        self.flags = None
+        self.rebuilds = 0
+
+    def update(self, lists, flags=None):
+        """Point the table at ``lists`` (n_lists sequences of equal length).
+
+        Returns True when the device copy had to be rebuilt.  ``flags`` is an
+        optional sequence of per-tensor APEX_B200_TF_* ints.  A ``None`` tensor
+        is allowed in lists a kernel will not dereference (address 0).
+        """
+        assert len(lists) == self.n_lists
+        n = len(lists[0])
+        ptrs = np.empty(self.n_lists * n, dtype=np.uint64)
+        for l, lst in enumerate(lists):
+            assert len(lst) == n
+            ptrs[l * n:(l + 1) * n] = [0 if t is None else t.data_ptr() for t in lst]
+        numels = np.fromiter((t.numel() for t in lists[0]), dtype=np.int64, count=n)
+        fl = np.zeros(n, dtype=np.int32) if flags is None else np.asarray(flags, dtype=np.int32)
+        key = (ptrs.tobytes(), numels.tobytes(), fl.tobytes())
+        if getattr(_C, "keep_table_refs", False):
+            self.lists = [list(l) for l in lists]
+            self.flags = fl
+        if key == self._key:
+            return False
+        self._key = key
+        self.n = n
+        self.total_numel = int(numels.sum())
+        self._pack(n, ptrs, numels, fl)
+        self.rebuilds += 1
+        return True
+
+    def _pack(self, n, ptrs, numels, fl):
+        nbytes = _C.table_bytes(n, self.n_lists)
+        on_gpu = self.device.type == "cuda"
+        if self._host is None or self._host.numel() < nbytes:
+            cap = max(nbytes, 4096)
+            self._host = torch.empty(cap, dtype=torch.uint8, pin_memory=on_gpu)
+            self._dev = torch.empty(cap, dtype=torch.uint8, device=self.device) if on_gpu else self._host
+            self._copied = None
+        if self._copied is not None:
+            self._copied.synchronize()   # previous upload still reading the staging buffer
+        self.struct = _C.table_pack(self._host.data_ptr(), self._host.numel(), n, self.n_lists,
+                                    numels.ctypes.data, ptrs.ctypes.data, fl.ctypes.data, self.chunk_elems)
+        if on_gpu:
+            self._dev[:nbytes].copy_(self._host[:nbytes], non_blocking=True)
+            self._copied = torch.cuda.Event()
+            self._copied.record()
+        self.struct.d_table = self._dev.data_ptr()
+        import ctypes
+        self.ref = ctypes.byref(self.struct)
+
+    def invalidate(self):
+        self._key = None
+
+
+def new_flag(device):
+    """The single device word every overflow check of one optimizer writes to."""
+    return torch.zeros(1, dtype=torch.int32, device=device)

@@ -1,0 +1,2 @@
+"""reference: apex/parallel/__init__.py:1"""
+from .distributed import DistributedDataParallel, Reducer

@@ -1,0 +1,458 @@
+"""Data-parallel gradient averaging (reference: apex/parallel/distributed.py).
+
+Observable behaviour is the reference's: parameters broadcast from rank 0 at
+construction; gradients bucketed per dtype in the order their hooks fire on
+rank 0, a bucket being cut once it holds >= ``message_size`` ELEMENTS, leftovers
+appended half -> float -> double; the structure broadcast as one int32 vector;
+buckets reduced strictly in index order on a side stream while backward keeps
+running; sum across ranks, then divide by the world size in the bucket's own
+dtype; the same three sanity errors.  The code is organised differently:
+
+* ``_BucketLayout`` -- the learned structure (what rank 0 dictates).
+* ``_BucketRound``  -- per-backward progress (which slots are filled, what may go).
+* ``_FlatSlot``     -- a persistent coalesced buffer + device tensor table per
+  bucket, so that the data path of one bucket is
+      1 gather launch -> NCCL collective -> 1 (x 1/world, scatter, inf/NaN check) launch
+  instead of the reference's alloc + cat + allreduce + divide + n copy_ launches
+  (distributed.py:11-23).  A bucket of a single tensor is reduced in place.
+"""
+import copy
+from collections import OrderedDict
+
+import torch
+import torch.distributed as dist
+from torch.autograd import Variable
+from torch.nn.modules import Module
+
+from .. import _C
+from ..multi_tensor import TensorTable, CHUNK_STREAM
+
+# bucket class per dtype; leftovers are appended in this order (reference :154-156, :178-180)
+_DTYPE_CLASS = {torch.float16: 0, torch.float32: 1, torch.float64: 2}
+
+
+# ---------------------------------------------------------------------------
+# flat collective on a list of tensors
+# ---------------------------------------------------------------------------
+
+class _FlatSlot(object):
+    """Coalesced staging buffer and tensor table, reused across iterations."""
+
+    __slots__ = ("table", "flat")
+
+    def __init__(self):
+        self.table = None
+        self.flat = None
+
+    def bind(self, tensors):
+        head = tensors[0]
+        if head.dtype not in _DTYPE_CLASS:
+            raise TypeError("apex_b200: unsupported bucket dtype %s" % head.dtype)
+        total = 0
+        for t in tensors:
+            if t.dtype != head.dtype or t.device != head.device:
+                raise TypeError("apply_flat_dist_call needs tensors of one type, got %s and %s"
+                                % (head.type(), t.type()))
+            if not t.is_contiguous():
+                raise RuntimeError("apex_b200: bucket tensors must be contiguous")
+            total += t.numel()
+        if self.table is None or self.table.device != head.device:
+            self.table = TensorTable(head.device, 1, CHUNK_STREAM)
+        if self.flat is None or self.flat.numel() != total or self.flat.dtype != head.dtype \
+                or self.flat.device != head.device:
+            self.flat = torch.empty(total, dtype=head.dtype, device=head.device)
+        self.table.update([tensors])
+        return self.flat
+
+
+_recent_slots = OrderedDict()
+_RECENT_MAX = 64
+
+
+def _recent_slot(tensors):
+    head = tensors[0]
+    key = (str(head.device), head.dtype, len(tensors), head.data_ptr())
+    slot = _recent_slots.pop(key, None)
+    if slot is None:
+        slot = _FlatSlot()
+    _recent_slots[key] = slot
+    while len(_recent_slots) > _RECENT_MAX:
+        _recent_slots.popitem(last=False)
+    return slot
+
+
+def apply_flat_dist_call(bucket, call, extra_args=None, _slot=None, _flag=None):
+    """Run collective ``call`` on the concatenation of ``bucket`` and write the result
+    back into the bucket's tensors; for ``dist.all_reduce`` the sum is then divided
+    by the world size (sum first, divide after, in the bucket dtype -- a sum that
+    overflows fp16 has to stay inf).  reference: distributed.py:11-23.
+
+    ``_slot`` (a persistent ``_FlatSlot``) and ``_flag`` (device word raised when
+    an averaged value is inf/NaN) are internal.
+    """
+    if len(bucket) == 0:
+        return
+    args = () if extra_args is None else tuple(extra_args)
+    averaging = call is dist.all_reduce
+
+    if len(bucket) == 1 and bucket[0].is_contiguous():
+        # nothing to coalesce: reduce the tensor where it lives
+        only = bucket[0]
+        call(only, *args)
+        if averaging:
+            _C.scale_flat(only.view(-1), dist.get_world_size(), _flag)
+        return
+
+    slot = _slot if _slot is not None else _recent_slot(bucket)
+    flat = slot.bind(bucket)
+    _C.mt_flatten(slot.table, 0, flat)
+    call(flat, *args)
+    if averaging:
+        _C.mt_scale_unflatten(slot.table, flat, 0, dist.get_world_size(), True, _flag)
+    else:
+        _C.mt_scale_unflatten(slot.table, flat, 0, 1.0, False, None)
+
+
+def flat_dist_call(tensors, call, extra_args=None):
+    """One flat call per tensor type, types taken in first-seen order.
+    reference: distributed.py:27-38"""
+    flat_dist_call.warn_on_half = True
+    per_type = OrderedDict()
+    for t in tensors:
+        per_type.setdefault(t.type(), []).append(t)
+    for same_type in per_type.values():
+        apply_flat_dist_call(same_type, call, extra_args)
+
+
+def extract_tensors(maybe_tensor, tensor_list):
+    """Append every tensor found in a (nested) iterable.  reference: distributed.py:41-49"""
+    if torch.is_tensor(maybe_tensor):
+        tensor_list.append(maybe_tensor)
+        return
+    try:
+        children = iter(maybe_tensor)
+    except TypeError:
+        return
+    for child in children:
+        extract_tensors(child, tensor_list)
+
+
+class Reducer(object):
+    """Averaging on demand: nothing is communicated until ``reduce()``.
+
+    Built from a module, its parameters are broadcast from rank 0 and ``reduce()``
+    averages their gradients; built from an iterable of tensors, ``reduce()``
+    averages those tensors.  reference: distributed.py:52-93
+    """
+
+    def __init__(self, module_or_grads_list):
+        if isinstance(module_or_grads_list, Module):
+            self.module = module_or_grads_list
+            flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,))
+        else:
+            self.module = None
+            self.grads = []
+            extract_tensors(module_or_grads_list, self.grads)
+
+    def reduce(self):
+        if self.module:
+            tensors = [p.grad.data for p in self.module.parameters() if p.grad is not None]
+        else:
+            tensors = self.grads
+        flat_dist_call(tensors, dist.all_reduce)
+
+
+# ---------------------------------------------------------------------------
+# bucket bookkeeping
+# ---------------------------------------------------------------------------
+
+class _BucketLayout(object):
+    """Which parameter sits where: ``members[b][loc]`` is an index into the list of
+    active parameters.  Built on every rank from its own hook order, then replaced
+    by rank 0's through ``encode``/``decode`` (reference: distributed.py:176-203)."""
+
+    def __init__(self, message_size):
+        self.message_size = message_size
+        self.members = []                 # closed buckets
+        self.open = [[], [], []]          # running bucket per dtype class
+        self.open_numel = [0, 0, 0]
+
+    def arrive(self, dtype_class, param_index, numel):
+        """A gradient became ready while the structure is being learned (reference :250-261)."""
+        self.open[dtype_class].append(param_index)
+        self.open_numel[dtype_class] += numel
+        if self.open_numel[dtype_class] >= self.message_size:
+            self.members.append(self.open[dtype_class])
+            self.open[dtype_class] = []
+            self.open_numel[dtype_class] = 0
+
+    def close(self):
+        for leftover in self.open:
+            if leftover:
+                self.members.append(leftover)
+        self.open = [[], [], []]
+        self.open_numel = [0, 0, 0]
+
+    def encode(self):
+        """[num_buckets] + sizes + members, the vector the reference broadcasts (:185-187)."""
+        out = [len(self.members)] + [len(b) for b in self.members]
+        for b in self.members:
+            out.extend(b)
+        return out
+
+    def decode(self, info):
+        n = info[0]
+        sizes = info[1:n + 1]
+        body = info[n + 1:]
+        self.members, at = [], 0
+        for size in sizes:
+            self.members.append(list(body[at:at + size]))
+            at += size
+
+    @property
+    def sizes(self):
+        return [len(b) for b in self.members]
+
+    def positions(self):
+        """param index -> (bucket_idx, bucket_loc)"""
+        where = {}
+        for b, bucket in enumerate(self.members):
+            for loc, param_index in enumerate(bucket):
+                where[param_index] = (b, loc)
+        return where
+
+
+class _BucketRound(object):
+    """Progress of one backward pass through a fixed layout."""
+
+    def __init__(self, sizes):
+        self.sizes = sizes
+        self.grads = [[None] * n for n in sizes]
+        self.filled = [0] * len(sizes)
+        self.next_bucket = 0
+        self.parked = set()               # full, but an earlier bucket is not
+
+    def put(self, bucket_idx, bucket_loc, grad):
+        """Store a ready gradient; returns the bucket indices that may be reduced now,
+        in the order they must be issued (identical on every rank)."""
+        row = self.grads[bucket_idx]
+        if row[bucket_loc] is not None:
+            raise RuntimeError("The backward pass is attempting to replace an already-filled "
+                               "bucket slot.  This is almost certainly an error.")
+        row[bucket_loc] = grad
+        self.filled[bucket_idx] += 1
+        if self.filled[bucket_idx] != self.sizes[bucket_idx]:
+            return []
+        if bucket_idx != self.next_bucket:
+            self.parked.add(bucket_idx)
+            return []
+        go = [bucket_idx]
+        self.next_bucket += 1
+        for waiting in sorted(self.parked):
+            if waiting > self.next_bucket:
+                break
+            if waiting < self.next_bucket:
+                raise ValueError("i should always be >= next_bucket")
+            go.append(waiting)
+            self.parked.remove(waiting)
+            self.next_bucket += 1
+        return go
+
+    def verify_complete(self):
+        if self.next_bucket != len(self.sizes):
+            raise RuntimeError("In epilogue, next_bucket != num_buckets.  "
+                               "This probably indicates some buckets were not allreduced.")
+        for have, want in zip(self.filled, self.sizes):
+            if have != want:
+                raise RuntimeError("Some param buckets were not allreduced.")
+
+
+# ---------------------------------------------------------------------------
+# the module wrapper
+# ---------------------------------------------------------------------------
+
+class DistributedDataParallel(Module):
+    """Wraps ``module``; gradients are averaged over all processes during ``backward()``,
+    overlapped with the rest of backward.
+
+    Args (reference: distributed.py:96-124):
+        module: the network.
+        message_size: minimum number of elements per communication bucket (default 1e7).
+        delay_allreduce: communicate only once backward has finished (no overlap).
+        shared_param: retired option; any value but None raises ValueError.
+    """
+
+    def __init__(self, module, message_size=10000000, delay_allreduce=False, shared_param=None):
+        super(DistributedDataParallel, self).__init__()
+
+        # the reference looks for dist.DistBackend / dist.dist_backend (both removed
+        # from torch since); all it needs is the backend name
+        self._backend = dist.get_backend()
+        self.backend_enum_holder = dist.Backend
+        self.warn_on_half = self._backend == dist.Backend.GLOO
+
+        if shared_param is not None:
+            raise ValueError("shared_param is no longer supported as an option.  It was misleadingly named from the start.  It turns out overlapping communication with computation should work fine with shared parameters.  If you still wish to delay communication to the end of the backward pass, use delay_allreduce=True|False instead.")
+
+        self.delay_allreduce = delay_allreduce
+        self.message_size = message_size
+        self.reduction_stream = torch.cuda.Stream()
+        self.module = module
+
+        if self._backend == dist.Backend.NCCL:
+            for p in self.module.parameters():
+                assert p.is_cuda, "NCCL backend only supports model parameters to be on GPU."
+
+        self.active_params = []
+        self.needs_refresh = True
+        self.callback_queued = False
+        self._layout = None
+        self._round = None
+        self._where = {}          # id(param) -> (bucket_idx, bucket_loc)
+        self._index_of = {}       # id(param) -> index in active_params
+        self._slots = {}
+
+        self.create_hooks()
+        flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,))
+
+    # ---- views of the structure under the reference's attribute names ---------------
+
+    @property
+    def num_buckets(self):
+        return 0 if self._layout is None else len(self._layout.members)
+
+    @property
+    def bucket_sizes(self):
+        return [] if self._layout is None else self._layout.sizes
+
+    @property
+    def buckets(self):
+        if self._round is not None:
+            return self._round.grads
+        return [] if self._layout is None else self._layout.members
+
+    @property
+    def param_id_to_bucket(self):
+        return self._where
+
+    @property
+    def next_bucket(self):
+        return 0 if self._round is None else self._round.next_bucket
+
+    # ---- pickling: a CUDA stream cannot be pickled (reference :163-172) -------------
+
+    def __getstate__(self):
+        state = copy.copy(self.__dict__)
+        for transient in ("reduction_stream", "_slots", "_round"):
+            state.pop(transient, None)
+        return state
+
+    def __setstate__(self, state):
+        super(DistributedDataParallel, self).__setstate__(state)
+        self.reduction_stream = torch.cuda.Stream()
+        self._slots = {}
+        self._round = None
+
+    # ---- structure ---------------------------------------------------------------------
+
+    def sync_bucket_structure(self):
+        """Finish this rank's layout, then take rank 0's (reference: distributed.py:176-203)."""
+        self._layout.close()
+        mine = self._layout.encode()
+        device = next(self.module.parameters()).device
+        info = torch.tensor(mine, dtype=torch.int32, device=device)
+        dist.broadcast(info, 0)
+        self._layout.decode(info.tolist())      # one device-to-host copy for the whole vector
+        self._where = {id(self.active_params[i]): pos for i, pos in self._layout.positions().items()}
+        self._slots = {}
+
+    # ---- hooks ---------------------------------------------------------------------------
+
+    def create_hooks(self):
+        """Hook every trainable parameter's gradient accumulator (reference: :206-276)."""
+        self.grad_accs = []
+        for param in self.module.parameters():
+            if param.requires_grad:
+                # a leaf's AccumulateGrad node is the first input of any trivial view of it
+                accumulator = param.expand_as(param).grad_fn.next_functions[0][0]
+                accumulator.register_hook(self._make_hook(param))
+                self.grad_accs.append(accumulator)
+
+    def _make_hook(self, param):
+        def on_grad_ready(*unused):
+            self._grad_ready(param)
+        return on_grad_ready
+
+    def _queue_once(self, callback):
+        if not self.callback_queued:
+            Variable._execution_engine.queue_callback(callback)
+            self.callback_queued = True
+
+    def _grad_ready(self, param):
+        learning = self.delay_allreduce or self.needs_refresh
+        if learning:
+            if not self.delay_allreduce:
+                self._layout.arrive(_DTYPE_CLASS[param.dtype], self._index_of[id(param)], param.numel())
+            self._queue_once(self._finish_backward_flat)
+        else:
+            self._queue_once(self._finish_backward_overlapped)
+            self.comm_ready_buckets(param)
+
+    def _finish_backward_flat(self):
+        """End of a backward that did no overlapped communication: adopt the bucket
+        structure if one was being learned, then one flat allreduce per dtype over
+        every gradient (reference ``allreduce_params``: :211-221)."""
+        if not self.delay_allreduce and self.needs_refresh:
+            self.sync_bucket_structure()
+            self.needs_refresh = False
+        grads = [p.grad.data for p in self.module.parameters() if p.grad is not None]
+        flat_dist_call(grads, dist.all_reduce)
+
+    def _finish_backward_overlapped(self):
+        """reference ``overlapping_backward_epilogue``: :223-233"""
+        torch.cuda.current_stream().wait_stream(self.reduction_stream)
+        self._round.verify_complete()
+
+    def comm_ready_buckets(self, param):
+        """``param``'s gradient is final: file it, and reduce whatever became eligible on
+        the side stream (reference: :279-315)."""
+        bucket_idx, bucket_loc = self._where[id(param)]
+        eligible = self._round.put(bucket_idx, bucket_loc, param.grad.data)
+        if not eligible:
+            return
+        # the gradients were produced on the current stream
+        self.reduction_stream.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(self.reduction_stream):
+            for b in eligible:
+                slot = self._slots.get(b)
+                if slot is None:
+                    slot = self._slots[b] = _FlatSlot()
+                apply_flat_dist_call(self._round.grads[b], dist.all_reduce, _slot=slot)
+
+    # ---- forward -----------------------------------------------------------------------------
+
+    def forward(self, *inputs, **kwargs):
+        """Run the wrapped module and arm the bookkeeping for the coming backward
+        (reference: :318-351)."""
+        result = self.module(*inputs, **kwargs)
+
+        if not self.delay_allreduce:
+            trainable = [p for p in self.module.parameters() if p.requires_grad]
+            # only forward may ask for a refresh; only the end of backward clears it
+            changed = (not self.active_params) or len(trainable) != len(self.active_params) or \
+                any(a is not b for a, b in zip(trainable, self.active_params))
+            if changed:
+                self.needs_refresh = True
+
+            if self.needs_refresh:
+                self._layout = _BucketLayout(self.message_size)
+                self._round = None
+                self._where = {}
+                self._index_of = {id(p): i for i, p in enumerate(trainable)}
+            else:
+                self._round = _BucketRound(self._layout.sizes)
+
+            self.active_params = trainable
+
+        self.callback_queued = False
+        return result
