@@ -316,6 +316,7 @@ class FP16_Optimizer(object):
                     master.grad = None
             if not srcs:
                 continue
+            self._ensure_device(srcs[0])
             table = self._grad_tables.get(gi)
             if table is None:
                 table = self._grad_tables[gi] = TensorTable(self._device, 2, CHUNK_STREAM)

@@ -154,10 +154,10 @@ int apex_b200_mt_zero(const apex_b200_mt_table* t, int list, int elem_size,
 /* Lists: 0 = grad (fp16, or fp32 with TF_GRAD_F32), 1 = fp32 master param,
  * 2 = fp32 momentum buffer, 3 = fp16 model param (ignored with TF_NO_MODEL).
  * Replaces, in one pass that reads every byte once:
- *   model_grads_to_master_grads (fp16util.py:93-112), _downscale_master
- *   (fp16_optimizer.py:236-241), the inner torch.optim.SGD step
- *   (fp16_optimizer.py:380 -> torch/optim/sgd.py:383-473) and
- *   master_params_to_model_params (fp16util.py:115-129).
+ *   model_grads_to_master_grads (apex/fp16_utils/fp16util.py:93-112),
+ *   _downscale_master (apex/fp16_utils/fp16_optimizer.py:236-241), the inner
+ *   torch.optim.SGD step (fp16_optimizer.py:380 -> torch/optim/sgd.py:383-473)
+ *   and master_params_to_model_params (apex/fp16_utils/fp16util.py:115-129).
  * Arithmetic order and FMA placement follow torch's CUDA foreach kernels.
  * The whole launch is a no-op when d_flag != NULL and *d_flag != 0
  * (the skipped step of fp16_optimizer.py:372-375). */
@@ -173,8 +173,9 @@ int apex_b200_mt_fused_sgd(const apex_b200_mt_table* t,
                            const int32_t* d_flag, void* stream);
 
 /* Lists: 0 = grad, 1 = fp32 master, 2 = exp_avg, 3 = exp_avg_sq, 4 = fp16 model.
- * Same fusion for torch.optim.Adam / AdamW (torch/optim/adam.py:416-547,
- * foreach branch :757-800).  step_size = (lr / bias_correction1) * -1 and
+ * Same fusion, with the same reference lines (apex/fp16_utils/fp16util.py:93-129,
+ * apex/fp16_utils/fp16_optimizer.py:236-241, :372-380), for an inner
+ * torch.optim.Adam / AdamW (torch/optim/adam.py:416-547, foreach branch :757-800).  step_size = (lr / bias_correction1) * -1 and
  * bias_correction2_sqrt are computed by the caller in python doubles exactly
  * as torch does. */
 typedef struct apex_b200_adam_args {
@@ -208,8 +209,10 @@ int apex_b200_mt_scale_unflatten(const apex_b200_mt_table* t, const void* flat,
                                  int dst_list, int dtype, double divisor,
                                  int apply_mul, int32_t* d_flag, void* stream);
 
-/* In-place `flat /= divisor` on one contiguous buffer (Reducer / callers that
- * keep the flat tensor): same arithmetic as above. */
+/* In-place `flat /= divisor` on one contiguous buffer: the
+ * `coalesced /= dist.get_world_size()` of apex/parallel/distributed.py:20 for a
+ * bucket that holds a single tensor (nothing to gather or scatter).  Same
+ * arithmetic and check as above. */
 int apex_b200_scale_flat(void* flat, int64_t numel, int dtype, double divisor,
                          int32_t* d_flag, void* stream);
 
@@ -227,7 +230,8 @@ int apex_b200_mt_l2norm(const apex_b200_mt_table* t, int grad_list,
                         double inv_scale, int apply_scale, float* d_partials,
                         int64_t partials_len, float* d_norm, void* stream);
 
-/* In-place `g *= clip_coef` for fp32 gradients where
+/* Second half of clip_master_grads (apex/fp16_utils/fp16_optimizer.py:263):
+ * in-place `g *= clip_coef` for fp32 gradients where
  * clip_coef = max_norm / (*d_norm + 1e-6), applied only when clip_coef < 1
  * (torch's clip_grad_norm_ clamps the coefficient to 1).  Reads the norm from
  * device memory: no host sync. */

@@ -1,0 +1,147 @@
+"""The C ABI: the library loads, exports exactly what include/apex_b200.h declares, and
+its host-only entry points (no GPU needed) behave.  No compute call is made here."""
+import ctypes
+import os
+import re
+import struct
+import subprocess
+
+import numpy as np
+import pytest
+import torch
+
+from apex_b200 import _C
+from tests.conftest import ROOT
+
+HEADER = os.path.join(ROOT, "include", "apex_b200.h")
+
+
+def declared_symbols():
+    text = open(HEADER).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(apex_b200_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_header_and_library_agree():
+    declared = declared_symbols()
+    assert len(declared) >= 18
+    out = subprocess.check_output(["nm", "-D", "--defined-only", _C.LIB_PATH]).decode()
+    exported = sorted(set(re.findall(r"\bT (apex_b200_[a-z0-9_]+)", out)))
+    assert exported == declared
+    # and the python binding binds every one of them
+    assert sorted(_C.SIGNATURES) == declared
+    for name in declared:
+        assert getattr(_C.lib, name) is not None
+
+
+def test_every_declaration_cites_the_reference():
+    text = open(HEADER).read()
+    # each entry point that replaces reference behaviour names the file it replaces
+    names = declared_symbols()
+    starts = sorted((text.rindex(" " + n + "("), n) for n in names)
+    for k, (at, name) in enumerate(starts):
+        if name in ("apex_b200_version", "apex_b200_error_string", "apex_b200_device_info",
+                    "apex_b200_mt_table_bytes", "apex_b200_mt_table_pack", "apex_b200_flag_clear"):
+            continue
+        # everything between the previous declaration and this one (comment + any struct)
+        comment = text[starts[k - 1][0]:at]
+        assert "apex/" in comment, name
+
+
+def test_version_and_error_strings():
+    assert _C.version() == 100
+    assert _C.error_string(0) == "ok"
+    assert "invalid argument" in _C.error_string(-1)
+    assert "maximum" in _C.error_string(-2)
+    assert "too small" in _C.error_string(-3)
+    assert isinstance(_C.error_string(700), str)       # cudaErrorIllegalAddress
+
+
+def _pack(numels, n_lists, ptrs, flags, chunk):
+    n = len(numels)
+    nbytes = _C.table_bytes(n, n_lists)
+    buf = np.zeros(nbytes, np.uint8)
+    st = _C.table_pack(buf.ctypes.data, nbytes, n, n_lists,
+                       np.asarray(numels, np.int64).ctypes.data if n else None,
+                       np.asarray(ptrs, np.uint64).ctypes.data if n else None,
+                       None if flags is None else np.asarray(flags, np.int32).ctypes.data, chunk)
+    return st, buf
+
+
+def test_table_pack_layout_ragged_and_empty():
+    numels = [5, 0, 2048 * 8 + 3, 16384, 0, 1]
+    n, L, chunk = len(numels), 2, 16384
+    ptrs = [4096 * (i + 1) for i in range(n)] + [4096 * 100 + 32 * i for i in range(n)]
+    ptrs[2] += 16                       # not 32 B aligned -> TF_UNALIGNED on tensor 2
+    flags = [0, 1, 2, 4, 0, 16]
+    st, buf = _pack(numels, L, ptrs, flags, chunk)
+    assert (st.n_tensors, st.n_lists, st.chunk_elems) == (n, L, chunk)
+    header = np.frombuffer(buf, np.int32, 4, 0)
+    off = 16
+    t_numel = np.frombuffer(buf, np.int64, n, off); off += 8 * n
+    t_start = np.frombuffer(buf, np.int64, n + 1, off); off += 8 * (n + 1)
+    t_ptr = np.frombuffer(buf, np.int64, n * L, off); off += 8 * n * L
+    t_flags = np.frombuffer(buf, np.int32, n, off); off += 4 * n
+    off = (off + 7) & ~7
+    t_chunk = np.frombuffer(buf, np.int32, n + 1, off)
+    assert t_numel.tolist() == numels
+    assert t_start.tolist() == [0, 5, 5, 5 + 16387, 5 + 16387 + 16384, 5 + 16387 + 16384, 5 + 16387 + 16384 + 1]
+    assert t_ptr.tolist() == ptrs
+    chunks = [1, 0, 2, 1, 0, 1]
+    assert t_chunk.tolist() == [0, 1, 1, 3, 4, 4, 5]
+    assert st.total_chunks == sum(chunks) == header[3]
+    want_flags = list(flags)
+    want_flags[2] |= _C.TF_UNALIGNED
+    assert t_flags.tolist() == want_flags
+    assert header.tolist() == [n, L, chunk, 5]
+
+
+def test_table_pack_rejects_bad_arguments():
+    buf = np.zeros(4096, np.uint8)
+    one = np.array([8], np.int64)
+    ptr = np.array([256], np.uint64)
+    out = _C.MtTableStruct()
+    call = _C.lib.apex_b200_mt_table_pack
+    ok = call(buf.ctypes.data, 4096, 1, 1, one.ctypes.data, ptr.ctypes.data, None, 2048, ctypes.byref(out))
+    assert ok == 0 and out.total_chunks == 1
+    assert call(buf.ctypes.data, 4096, 1, 1, one.ctypes.data, ptr.ctypes.data, None, 1000, ctypes.byref(out)) == -1
+    assert call(buf.ctypes.data, 8, 1, 1, one.ctypes.data, ptr.ctypes.data, None, 2048, ctypes.byref(out)) == -3
+    assert call(None, 4096, 1, 1, one.ctypes.data, ptr.ctypes.data, None, 2048, ctypes.byref(out)) == -1
+    neg = np.array([-1], np.int64)
+    assert call(buf.ctypes.data, 4096, 1, 1, neg.ctypes.data, ptr.ctypes.data, None, 2048, ctypes.byref(out)) == -1
+    # empty table is fine
+    assert call(buf.ctypes.data, 4096, 0, 1, None, None, None, 2048, ctypes.byref(out)) == 0
+    assert out.total_chunks == 0
+
+
+def test_null_arguments_are_rejected_without_touching_cuda():
+    lib = _C.lib
+    assert lib.apex_b200_mt_check_overflow(None, 0, None, None) == -1
+    assert lib.apex_b200_mt_fused_sgd(None, None, None, None) == -1
+    assert lib.apex_b200_mt_fused_adam(None, None, None, None) == -1
+    assert lib.apex_b200_flag_clear(None, None) == -1
+    t = _C.MtTableStruct(None, 0, 1, 2048, 0)
+    # an empty table is a successful no-op for every kernel entry point
+    assert lib.apex_b200_mt_unscale(ctypes.byref(t), 0, 1.0, None, 0, None) == 0
+    assert lib.apex_b200_mt_zero(ctypes.byref(t), 0, 2, None) == 0
+    assert lib.apex_b200_mt_unscale(ctypes.byref(t), 3, 1.0, None, 0, None) == -1     # list out of range
+    assert lib.apex_b200_scale_flat(None, 0, 0, 2.0, None, None) == 0
+    assert lib.apex_b200_scale_flat(None, 10, 7, 2.0, None, None) == -1
+
+
+def test_product_fails_loudly_without_the_library(tmp_path):
+    """No CPU fallback: importing the binding without the .so is an ImportError."""
+    code = ("import importlib.util, sys; sys.path.insert(0, %r);"
+            "import apex_b200._C as c" % ROOT)
+    # run in a subprocess with LIB_PATH pointing nowhere
+    probe = ("import sys; sys.path.insert(0, %r)\n"
+             "import os, importlib\n"
+             "real = os.path.exists\n"
+             "os.path.exists = lambda p: False if p.endswith('libapex_b200.so') else real(p)\n"
+             "try:\n"
+             "    import apex_b200._C\n"
+             "    print('IMPORTED')\n"
+             "except ImportError as e:\n"
+             "    print('IMPORTERROR', 'no python or CPU' in str(e))\n" % ROOT)
+    out = subprocess.check_output(["python", "-c", probe]).decode()
+    assert "IMPORTERROR True" in out

@@ -1,0 +1,227 @@
+"""apex_b200.parallel on CPU under gloo: bucket structure, ordering, averaging, N > 1.
+
+Host-side logic only (the kernel wrappers are the oracle-backed double).  The
+world_size-2 cases run as two spawned processes rendezvousing on 127.0.0.1.
+"""
+import os
+import socket
+import sys
+
+import numpy as np
+import pytest
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from tests.conftest import ROOT
+from tests.golden_cases import build_layout_model
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    port = s.getsockname()[1]
+    s.close()
+    return port
+
+
+@pytest.fixture
+def gloo_single(cpu_backend):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(_free_port())
+    dist.init_process_group("gloo", rank=0, world_size=1)
+    yield cpu_backend
+    dist.destroy_process_group()
+
+
+def test_bucket_layout_matches_reference(golden_json, gloo_single):
+    from apex_b200.parallel import DistributedDataParallel as DDP
+    for case in golden_json["ddp_layout"]:
+        model = build_layout_model(case["model"])
+        ddp = DDP(model, message_size=case["message_size"])
+        x = torch.randn(5, 6)
+        for it in range(3):
+            model.zero_grad()
+            y = ddp(x)
+            y.float().sum().backward()
+            assert ddp.needs_refresh is False
+        plist = [p for p in model.parameters() if p.requires_grad]
+        where = [list(ddp.param_id_to_bucket[id(p)]) for p in plist]
+        assert ddp.num_buckets == case["num_buckets"], case
+        assert list(ddp.bucket_sizes) == case["bucket_sizes"], case
+        assert where == case["param_to_bucket"], case
+        # world size 1: averaging is the identity, gradients must be untouched and finite
+        for p in plist:
+            assert torch.isfinite(p.grad.float()).all()
+
+
+def test_guards_and_options(gloo_single):
+    from apex_b200.parallel import DistributedDataParallel as DDP
+    from apex_b200.parallel.distributed import _BucketRound
+    model = build_layout_model("mlp3")
+    with pytest.raises(ValueError, match="shared_param is no longer supported"):
+        DDP(model, shared_param=True)
+    ddp = DDP(model)
+    assert ddp.message_size == 10000000 and ddp.delay_allreduce is False
+    assert ddp.module is model and ddp.reduction_stream is not None
+    r = _BucketRound([2, 1])
+    g = torch.zeros(1)
+    assert r.put(1, 0, g) == []              # full but not next: parked
+    assert r.put(0, 0, g) == []
+    with pytest.raises(RuntimeError, match="already-filled"):
+        r.put(0, 0, g)
+    with pytest.raises(RuntimeError, match="next_bucket != num_buckets"):
+        r.verify_complete()
+    assert r.put(0, 1, g) == [0, 1]          # 0 goes, then parked 1 drains, in index order
+    r.verify_complete()
+    r2 = _BucketRound([1, 2])
+    r2.put(0, 0, g)
+    r2.next_bucket = 2
+    r2.filled[1] = 1
+    with pytest.raises(RuntimeError, match="Some param buckets were not allreduced"):
+        r2.verify_complete()
+
+
+def test_delay_allreduce_and_refresh_on_param_change(gloo_single):
+    from apex_b200.parallel import DistributedDataParallel as DDP
+    model = build_layout_model("mlp3")
+    ddp = DDP(model, delay_allreduce=True)
+    ddp(torch.randn(2, 6)).sum().backward()
+    assert "flatten" in gloo_single.calls and ddp.num_buckets == 0      # no structure is ever learned
+    ddp2 = DDP(build_layout_model("mlp3"), message_size=50)
+    for _ in range(2):
+        ddp2(torch.randn(2, 6)).sum().backward()
+    assert ddp2.needs_refresh is False and ddp2.num_buckets == 3
+    # freezing a parameter changes the active list -> structure is learned again
+    ddp2.module[0].bias.requires_grad = False
+    ddp2.module.zero_grad()
+    ddp2(torch.randn(2, 6)).sum().backward()
+    assert ddp2.needs_refresh is False
+    assert sum(ddp2.bucket_sizes) == 5
+
+
+# ---- world size 2 -------------------------------------------------------------------------------
+
+def _install_double():
+    """fake_backend.install without pytest's monkeypatch (child process)."""
+    import contextlib as _ctx
+    from apex_b200 import _C
+    from tests import fake_backend as fb
+    _C.keep_table_refs = True
+    for name in ("flag_clear", "mt_check_overflow", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
+                 "mt_copy", "mt_zero", "mt_fused_sgd", "mt_fused_adam", "mt_flatten", "mt_scale_unflatten",
+                 "scale_flat", "mt_l2norm", "mt_clip_by_norm"):
+        setattr(_C, name, getattr(fb, name))
+    torch.cuda.Event = fb._Event
+    torch.cuda.Stream = fb._Stream
+    torch.cuda.current_stream = lambda *a, **k: fb._Stream()
+    torch.cuda.stream = lambda s: _ctx.nullcontext()
+    torch.Tensor.type = fb._cuda_named_type
+    return fb
+
+
+class _RaceModel(torch.nn.Module):
+    """The model of the reference's own known-answer test
+    (tests/distributed/ddp_race_condition_test.py:28-34), smaller."""
+
+    def __init__(self, n):
+        super(_RaceModel, self).__init__()
+        self.a = torch.nn.Parameter(torch.full((n,), 1.0))
+        self.b = torch.nn.Parameter(torch.full((n,), 2.0))
+
+    def forward(self, input):
+        return (input * self.a) * self.b
+
+
+def _worker(rank, world, port, out_dir):
+    sys.path.insert(0, ROOT)
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    fb = _install_double()
+    from apex_b200.parallel import DistributedDataParallel as DDP, Reducer
+    from apex_b200.parallel.distributed import flat_dist_call
+    ok = {}
+
+    # (7) of SURVEY 8c: flat_dist_call, fp16 [1,1,1] + [2,2,2] -> [1.5]*3 ; fp32 10 / 20 -> 15
+    h = torch.full((3,), float(rank + 1)).half()
+    f = torch.full((4,), 10.0 * (rank + 1))
+    h2 = torch.full((5,), float(rank + 1)).half()
+    flat_dist_call([h, f, h2], dist.all_reduce)
+    ok["flat_half"] = bool((h == 1.5).all() and (h2 == 1.5).all() and h.dtype == torch.float16)
+    ok["flat_float"] = bool((f == 15.0).all())
+
+    # fp16 sum that overflows must stay inf after the divide (sum first, divide after)
+    big = torch.full((4,), 40000.0).half()
+    flat_dist_call([big, big.clone()], dist.all_reduce)
+    ok["fp16_sum_overflow_stays_inf"] = bool(torch.isinf(big).all())
+
+    # the reference's known answer, message_size=1 so every parameter is its own bucket
+    n = 64
+    model = _RaceModel(n)
+    ddp = DDP(model, message_size=1)
+    x = torch.empty(n)
+    race = True
+    for i in range(6):
+        x.fill_(i + rank)
+        model.zero_grad()
+        ddp(x).sum().backward()
+        race &= model.a.grad.sum().item() == 2. * n * (2. * i + 1) / 2.
+        race &= model.b.grad.sum().item() == 1. * n * (2. * i + 1) / 2.
+    ok["race_known_answer"] = bool(race)
+    ok["race_buckets"] = ddp.num_buckets == 2
+
+    # a real model with rank-dependent data: averaged gradients == mean of the local gradients,
+    # in the learning iteration (one flat call per dtype) and in overlapped iterations alike
+    torch.manual_seed(0)
+    net = build_layout_model("mlp3")
+    ref = build_layout_model("mlp3")
+    if rank == 1:                      # rank 0's values must win at construction
+        for p in net.parameters():
+            p.data.add_(1.0)
+    ddp = DDP(net, message_size=50)
+    ok["broadcast_from_rank0"] = all(torch.equal(p.data, q.data) for p, q in zip(net.parameters(), ref.parameters()))
+    same = True
+    for it in range(4):
+        g = torch.Generator().manual_seed(100 * it + rank)
+        xb = torch.randn(7, 6, generator=g)
+        net.zero_grad()
+        ref.zero_grad()
+        ddp(xb).pow(2).sum().backward()
+        ref(xb).pow(2).sum().backward()
+        for p, q in zip(net.parameters(), ref.parameters()):
+            local = q.grad.clone()
+            dist.all_reduce(local)
+            want = local * torch.tensor(0.5)
+            same &= torch.equal(p.grad, want)
+    ok["ddp_average"] = bool(same)
+    ok["ddp_layout"] = (ddp.num_buckets, list(ddp.bucket_sizes))
+    ok["ddp_calls"] = sorted(set(fb.calls))
+
+    # Reducer on a list of tensors and on a module
+    t = [torch.full((3,), float(rank)), [torch.full((2,), 2.0 * rank).half()]]
+    red = Reducer(t)
+    red.reduce()
+    ok["reducer_list"] = bool((t[0] == 0.5).all() and (t[1][0] == 1.0).all())
+    m2 = torch.nn.Linear(3, 2)
+    red2 = Reducer(m2)
+    m2(torch.full((1, 3), float(rank + 1))).sum().backward()
+    red2.reduce()
+    ok["reducer_module"] = bool(torch.equal(m2.weight.grad, torch.full((2, 3), 1.5)))
+
+    torch.save(ok, os.path.join(out_dir, "rank%d.pt" % rank))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_world_size_two(tmp_path):
+    port = _free_port()
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    results = [torch.load(os.path.join(str(tmp_path), "rank%d.pt" % r), weights_only=False) for r in range(2)]
+    for r in results:
+        for key in ("flat_half", "flat_float", "fp16_sum_overflow_stays_inf", "race_known_answer", "race_buckets",
+                    "broadcast_from_rank0", "ddp_average", "reducer_list", "reducer_module"):
+            assert r[key] is True, (key, r)
+        assert {"flatten", "scale_unflatten", "scale_flat"} <= set(r["ddp_calls"])
+    # rank 0 dictates the structure: identical on both ranks
+    assert results[0]["ddp_layout"] == results[1]["ddp_layout"] == (3, [3, 1, 2])

@@ -1,0 +1,421 @@
+"""Host-side logic of the product package on CPU tensors.
+
+The kernels cannot run here; the `cpu_backend` fixture swaps the python kernel
+wrappers for an oracle-backed double (tests/fake_backend.py) so that everything
+ABOVE the C ABI -- tensor tables, lazy master gradients, the commit protocol for
+optimizer state, scaler trajectories, messages, checkpoints -- runs for real and is
+compared with what the unmodified reference produced (tests/golden).
+"""
+import contextlib
+import io
+
+import numpy as np
+import pytest
+import torch
+
+from tests.golden_cases import CASES, bits, grads_for, init_params, make_inner, tensor_from, ulp_diff
+
+
+def _drive(name, meta, arrays, backend, probe=None):
+    from apex_b200.fp16_utils import FP16_Optimizer
+    params = init_params(arrays, name)
+    inner = make_inner(meta)(params)
+    opt = FP16_Optimizer(inner, verbose=False, **meta["fp16_kwargs"])
+    rows, msgs, norms, m0 = [], [], [], []
+    for it in range(meta["iters"]):
+        for p, g in zip(params, grads_for(arrays, name, it, len(params))):
+            p.grad = g
+        buf = io.StringIO()
+        with contextlib.redirect_stdout(buf):
+            opt.update_master_grads()
+            if meta["clip"] is not None:
+                norms.append(float(opt.clip_master_grads(meta["clip"])))
+            if probe is not None:
+                probe(opt, it)
+            opt.step()
+        msgs.append(buf.getvalue())
+        ls = opt.loss_scaler
+        rows.append({"overflow": bool(opt.overflow), "loss_scale": float(opt.loss_scale),
+                     "cur_iter": getattr(ls, "cur_iter", None),
+                     "last_overflow_iter": getattr(ls, "last_overflow_iter", None)})
+        m0.append(opt.fp32_from_fp16_groups[0][0].data.numpy().copy())
+    return opt, rows, msgs, norms, m0
+
+
+@pytest.mark.parametrize("name", CASES)
+def test_fp16_optimizer_replays_reference(name, golden_json, golden_arrays, cpu_backend):
+    meta = golden_json[name]
+    adam = meta["optimizer"] in ("Adam", "AdamW")
+    opt, rows, msgs, norms, m0 = _drive(name, meta, golden_arrays, cpu_backend)
+    # decisions, trajectory and messages: bit-exact
+    assert rows == meta["rows"]
+    assert msgs == meta["messages"]
+    if meta["clip"] is not None:
+        assert norms == meta["norms"]
+    steps_taken = sum(1 for r in rows if not r["overflow"])
+    for i, (m, p) in enumerate(zip(opt.fp32_from_fp16_groups[0], opt.fp16_groups[0])):
+        want = golden_arrays["%s/final_master/%d" % (name, i)]
+        if not adam:
+            assert np.array_equal(m.data.numpy(), want), (name, i)
+            assert np.array_equal(bits(p.data), golden_arrays["%s/final_model/%d" % (name, i)])
+        else:
+            # the double computes Adam with torch's CUDA association, the golden run used torch's
+            # CPU kernels (other association, sqrt not correctly rounded): a few ulp at the
+            # parameter's scale per step.  Exact Adam parity is asserted on the GPU.
+            scale = np.maximum(np.abs(want), meta["opt_kwargs"]["lr"])
+            assert (np.abs(m.data.numpy() - want) <= 4 * steps_taken * np.spacing(scale.astype(np.float32))).all()
+        # the fp16 copy is always the rounding of the master next to it
+        assert torch.equal(p.data, m.data.half())
+        st = opt.optimizer.state[m]
+        gk = "%s/final_momentum_buffer/%d" % (name, i)
+        if gk in golden_arrays:
+            assert np.array_equal(st["momentum_buffer"].numpy(), golden_arrays[gk])
+        gk = "%s/final_step/%d" % (name, i)
+        if gk in golden_arrays:
+            assert float(st["step"]) == float(golden_arrays[gk]) == steps_taken
+    for i, p in enumerate(opt.fp32_from_fp32_groups[0]):
+        assert np.array_equal(p.data.numpy(), golden_arrays["%s/final_fp32/%d" % (name, i)])
+        assert np.array_equal(p.grad.data.numpy(), golden_arrays["%s/final_fp32_grad/%d" % (name, i)])
+    # which path ran
+    kinds = set(cpu_backend.calls)
+    assert ("fused_adam" if adam else "fused_sgd") in kinds
+    if meta["clip"] is None:
+        assert "grads_to_master" not in kinds        # master grads never had to be materialised
+    else:
+        assert "grads_to_master" in kinds
+
+
+def test_skipped_step_leaves_no_optimizer_state(golden_json, golden_arrays, cpu_backend):
+    """First iterations overflow at scale 2^32: the reference's inner optimizer has seen no
+    step, so its state must still be empty (momentum buffers are only published on commit)."""
+    name = "sgd_default_dynamic"
+    meta = golden_json[name]
+    seen = []
+
+    def probe(opt, it):
+        seen.append(len(opt.optimizer.state))
+    opt, rows, _, _, _ = _drive(name, meta, golden_arrays, cpu_backend, probe)
+    first_clean = [r["overflow"] for r in rows].index(False)
+    assert first_clean == 8
+    assert seen[:first_clean + 1] == [0] * (first_clean + 1)
+    assert len(opt.optimizer.state) == 6
+
+
+def test_master_grads_are_lazy_but_observable(cpu_backend):
+    from apex_b200.fp16_utils import FP16_Optimizer
+    p = torch.nn.Parameter((torch.arange(20, dtype=torch.float32) / 7).half())
+    opt = FP16_Optimizer(torch.optim.SGD([p], lr=0.5), static_loss_scale=3.0, verbose=False)
+    master = opt.fp32_from_fp16_groups[0][0]
+    assert master.dtype == torch.float32 and master.requires_grad and master.is_leaf
+    assert master.grad is None
+    p.grad = (torch.arange(20, dtype=torch.float32) - 4).half()
+    opt.update_master_grads()
+    assert "grads_to_master" not in cpu_backend.calls
+    # looking at the gradient makes it real: float(g16) * float(1/3.)
+    want = p.grad.float() * torch.tensor(1. / 3.0, dtype=torch.float32)
+    assert torch.equal(master.grad, want)
+    assert cpu_backend.calls.count("grads_to_master") == 1
+    master.grad            # second look does not launch again
+    assert cpu_backend.calls.count("grads_to_master") == 1
+    # a materialised gradient may be edited by the user; step() must use the edited values
+    master.grad.mul_(2.0)
+    before = master.data.clone()
+    opt.step()
+    assert torch.equal(master.data, before - 0.5 * (want * 2.0))
+    assert torch.equal(p.data, master.data.half())
+    # zero_grad: both gradients zeroed in ONE launch
+    n_zero = cpu_backend.calls.count("zero")
+    opt.zero_grad()
+    assert cpu_backend.calls.count("zero") == n_zero + 1
+    assert float(p.grad.abs().sum()) == 0 and float(master.grad.abs().sum()) == 0
+    opt.zero_grad(set_grads_to_None=True)
+    assert p.grad is None and master.grad is None
+
+
+def test_generic_inner_optimizer_takes_the_unfused_path(cpu_backend):
+    """An inner optimizer we have no fused kernel for (Adagrad) still works: gradients are
+    materialised, torch does the update, one launch refreshes the fp16 copies."""
+    from apex_b200.fp16_utils import FP16_Optimizer
+    from oracle import apex_ref
+    torch.manual_seed(3)
+    init = [(torch.randn(33) * 0.1).half(), (torch.randn(4, 5) * 0.1).half()]
+    grads = [[(torch.randn(t.shape) * 8).half() for t in init] for _ in range(3)]
+    ps = [torch.nn.Parameter(t.clone()) for t in init]
+    opt = FP16_Optimizer(torch.optim.Adagrad(ps, lr=0.1), static_loss_scale=8.0, verbose=False)
+    rs = [torch.nn.Parameter(t.clone()) for t in init]
+    ref = apex_ref.MixedPrecisionStep(rs, lambda q: torch.optim.Adagrad(q, lr=0.1), static_loss_scale=8.0)
+    for it in range(3):
+        for p, r, g in zip(ps, rs, grads[it]):
+            p.grad = g.clone()
+            r.grad = g.clone()
+        opt.update_master_grads()
+        opt.step()
+        ref.update_master_grads()
+        ref.step()
+    assert "fused_sgd" not in cpu_backend.calls and "fused_adam" not in cpu_backend.calls
+    assert "master_to_model" in cpu_backend.calls
+    for p, r, m, rm in zip(ps, rs, opt.fp32_from_fp16_groups[0], ref.masters):
+        assert torch.equal(m.data, rm.data)
+        assert torch.equal(p.data, r.data)
+
+
+def test_closure_step(cpu_backend):
+    from apex_b200.fp16_utils import FP16_Optimizer
+    p = torch.nn.Parameter(torch.ones(8).half())
+    opt = FP16_Optimizer(torch.optim.SGD([p], lr=0.25), static_loss_scale=4.0, verbose=False)
+    calls = []
+
+    def closure():
+        calls.append(1)
+        p.grad = torch.full((8,), 4.0).half()       # "scaled" gradient of 1.0
+        opt.update_master_grads()
+        return torch.tensor(1.0)
+    out = opt.step(closure)
+    assert len(calls) == 1 and float(out) == 1.0
+    assert torch.equal(p.data, torch.full((8,), 0.75).half())
+    assert opt.first_closure_call_this_step is True
+
+
+def test_constructor_contract(cpu_backend, capsys):
+    from apex_b200.fp16_utils import FP16_Optimizer, DynamicLossScaler, LossScaler
+    h = torch.nn.Parameter(torch.zeros(3).half())
+    f = torch.nn.Parameter(torch.zeros(2))
+    frozen = torch.nn.Parameter(torch.zeros(2).half(), requires_grad=False)
+    inner = torch.optim.SGD([h, f, frozen], lr=0.1, momentum=0.9)
+    opt = FP16_Optimizer(inner, dynamic_loss_scale=True, dynamic_loss_args={"init_scale": 8, "scale_window": 2})
+    out = capsys.readouterr().out
+    assert "FP16_Optimizer processing param group 0:" in out
+    assert "FP16_Optimizer received torch.cuda.HalfTensor with torch.Size([3])" in out
+    assert "FP16_Optimizer received torch.cuda.FloatTensor with torch.Size([2])" in out
+    assert opt.fp16_groups == [[h]] or (len(opt.fp16_groups[0]) == 1 and opt.fp16_groups[0][0] is h)
+    assert opt.fp32_from_fp32_groups[0][0] is f
+    assert inner.param_groups[0]["params"][0] is opt.fp32_from_fp16_groups[0][0]
+    assert inner.param_groups[0]["params"][1] is f
+    assert isinstance(opt.loss_scaler, DynamicLossScaler) and opt.loss_scale == 8
+    assert opt.overflow is False and opt.first_closure_call_this_step is True
+    opt.loss_scale = 4.0
+    assert opt.loss_scaler.cur_scale == 4.0
+    assert opt.param_groups is inner.param_groups and opt.state is inner.state
+    with pytest.raises(NotImplementedError):
+        opt.inspect_master_grad_data()
+    with pytest.raises(RuntimeError):
+        opt.__getstate__()
+    static = FP16_Optimizer(torch.optim.SGD([torch.nn.Parameter(torch.zeros(1).half())], lr=1.0),
+                            static_loss_scale=128.0, verbose=False)
+    assert isinstance(static.loss_scaler, LossScaler) and static.loss_scale == 128.0
+    with pytest.raises(TypeError, match="Wrapped parameters must be either"):
+        FP16_Optimizer(torch.optim.SGD([torch.nn.Parameter(torch.zeros(1).double())], lr=1.0), verbose=False)
+
+
+def test_state_dict_round_trip_and_pickle(cpu_backend, tmp_path):
+    from apex_b200.fp16_utils import FP16_Optimizer
+
+    def build():
+        torch.manual_seed(0)
+        ps = [torch.nn.Parameter((torch.randn(9) * 0.1).half()), torch.nn.Parameter((torch.randn(2, 3) * 0.1).half())]
+        return ps, FP16_Optimizer(torch.optim.SGD(ps, lr=0.1, momentum=0.9), dynamic_loss_scale=True,
+                                  dynamic_loss_args={"init_scale": 16., "scale_window": 3}, verbose=False)
+    ps, opt = build()
+    g = torch.Generator().manual_seed(5)
+    for it in range(4):
+        for p in ps:
+            p.grad = (torch.randn(p.shape, generator=g) * 16).half()
+        opt.update_master_grads()
+        opt.step()
+    sd = opt.state_dict()
+    assert sorted(sd) == ['dynamic_loss_scale', 'first_closure_call_this_step', 'fp32_from_fp16', 'loss_scaler',
+                          'optimizer_state_dict', 'overflow']
+    path = tmp_path / "ckpt.pt"
+    torch.save({"optimizer": sd, "model": [p.data for p in ps]}, str(path))
+    loaded = torch.load(str(path), weights_only=False)
+    # masters are stored as plain fp32 tensors, like the reference's
+    assert type(loaded["optimizer"]["fp32_from_fp16"][0][0]) is torch.Tensor
+    assert set(loaded["optimizer"]["loss_scaler"].__dict__) == {"cur_scale", "cur_iter", "last_overflow_iter",
+                                                                 "scale_factor", "scale_window"}
+    ps2, opt2 = build()
+    for p2, saved in zip(ps2, loaded["model"]):
+        p2.data.copy_(saved)
+    opt2.load_state_dict(loaded["optimizer"])
+    assert opt2.loss_scale == opt.loss_scale and opt2.loss_scaler.cur_iter == opt.loss_scaler.cur_iter
+    for a, b in zip(opt.fp32_from_fp16_groups[0], opt2.fp32_from_fp16_groups[0]):
+        assert torch.equal(a.data, b.data)
+    # both continue identically
+    for it in range(3):
+        gs = [(torch.randn(p.shape, generator=g) * 16).half() for p in ps]
+        for o, plist in ((opt, ps), (opt2, ps2)):
+            for p, gg in zip(plist, gs):
+                p.grad = gg.clone()
+            o.update_master_grads()
+            o.step()
+    for a, b in zip(opt.fp32_from_fp16_groups[0], opt2.fp32_from_fp16_groups[0]):
+        assert torch.equal(a.data, b.data)
+    for a, b in zip(ps, ps2):
+        assert torch.equal(a.data, b.data)
+
+
+def test_product_scalers_follow_reference_trajectories(golden_json):
+    from apex_b200.fp16_utils import DynamicLossScaler, LossScaler
+    g = golden_json["dyn_traj_small"]
+    s = DynamicLossScaler(init_scale=g["init_scale"], scale_window=g["scale_window"])
+    traj = []
+    for it in range(10):
+        s.update_scale(it in g["overflow_iters"])
+        traj.append(s.cur_scale)
+    assert traj == g["cur_scale"]
+    assert [type(x) for x in traj[:2]] == [int, int]          # python int until the first change
+    g = golden_json["dyn_traj_long"]
+    s = DynamicLossScaler(init_scale=g["init_scale"], scale_factor=2., scale_window=g["scale_window"])
+    for ov, row in zip(g["pattern"], g["rows"]):
+        s.update_scale(ov)
+        assert [float(s.cur_scale), s.cur_iter, s.last_overflow_iter] == row
+    s = DynamicLossScaler()
+    assert (s.cur_scale, s.scale_factor, s.scale_window, s.cur_iter, s.last_overflow_iter) == (2**32, 2., 1000, 0, -1)
+    growth, prev = [], s.cur_scale
+    for it in range(2100):
+        s.update_scale(False)
+        if s.cur_scale != prev:
+            growth.append(it)
+            prev = s.cur_scale
+    assert growth == golden_json["dyn_default_growth_calls"]
+    s = DynamicLossScaler(init_scale=2)
+    for _ in range(4):
+        s.update_scale(True)
+    assert s.cur_scale == 1 and isinstance(s.cur_scale, int)
+    st = LossScaler(128.0)
+    p = torch.nn.Parameter(torch.zeros(2))
+    p.grad = torch.tensor([float("inf"), 1.0])
+    assert st.has_overflow([p]) is False and st.loss_scale == 128.0
+    st.update_scale(True)
+    assert st.loss_scale == 128.0
+
+
+def test_product_has_overflow_known_answers(golden_json, cpu_backend):
+    from apex_b200.fp16_utils import DynamicLossScaler
+    g = golden_json["has_inf_or_nan"]
+    f = DynamicLossScaler._has_inf_or_nan
+    assert f(torch.tensor([float("inf"), -float("inf")])) == g["inf_and_neg_inf_f32"]
+    assert f(torch.tensor([1.0, float("nan")]).half()) == g["one_nan_f16"]
+    assert f(torch.full((1000000,), 65504.0).half()) == g["million_max_f16"]
+    assert f(torch.tensor([0.5, -float("inf"), 2.0]).half()) == g["neg_inf_f16"]
+    assert f(torch.randn(1000).half()) is False
+    s = DynamicLossScaler()
+    ps = [torch.nn.Parameter(torch.zeros(4).half()) for _ in range(3)]
+    assert s.has_overflow(ps) is False            # no grads at all
+    for p in ps:
+        p.grad = torch.ones(4).half()
+    assert s.has_overflow(ps) is False
+    ps[2].grad[1] = float("nan")
+    assert s.has_overflow(ps) is True
+
+
+def test_product_amp_scaler(golden_json, golden_arrays, cpu_backend):
+    from apex_b200.amp import LossScaler, scale_check_overflow
+    g = golden_json["amp_partial"]
+    ps = [torch.nn.Parameter(torch.zeros(2)) for _ in range(3)]
+    ps[0].grad = torch.tensor([4.0, 4.0])
+    ps[1].grad = torch.tensor([float("inf"), 4.0])
+    ps[2].grad = torch.tensor([4.0, 4.0])
+    sc = LossScaler()
+    assert sc.unscale_and_update([{"params": ps}], 4.0) == g["skip"]
+    assert [p.grad.tolist() for p in ps] == g["grads"]           # the reference's partial mutation
+    assert sc.loss_scale() == g["loss_scale_after"]
+    sc = LossScaler()
+    p = torch.nn.Parameter(torch.zeros(4))
+    seen = []
+    for it in range(2001):
+        p.grad = torch.ones(4)
+        sc.unscale_and_update([{"params": [p]}], 1.0)
+        if it in (1998, 1999, 2000):
+            seen.append(sc.loss_scale())
+    assert seen == golden_json["amp_growth"]["scale_after_calls_1999_2000_2001"]
+    sc = LossScaler()
+    sc._loss_scale, sc._unskipped = 2.**24, 1999
+    p.grad = torch.ones(4)
+    sc.unscale_and_update([{"params": [p]}], 1.0)
+    assert sc.loss_scale() == golden_json["amp_cap"]
+    sc = LossScaler()
+    for _ in range(20):
+        p.grad = torch.tensor([float("nan"), 1, 1, 1])
+        assert sc.unscale_and_update([{"params": [p]}], 1.0) is True
+    assert sc.loss_scale() == golden_json["amp_no_floor"]
+    x = tensor_from(golden_arrays["amp_unscale_in"])
+    assert scale_check_overflow(x, golden_json["amp_unscale_scale"]) is False
+    assert np.array_equal(x.numpy(), golden_arrays["amp_unscale_out"])
+    y = torch.tensor([1.0, float("nan")])
+    assert scale_check_overflow(y, 0.5) is True and y[0] == 1.0
+
+
+def test_amp_handle_and_optim_wrapper(cpu_backend):
+    from apex_b200.amp import AmpHandle, NoOpHandle
+    w = torch.nn.Parameter(torch.tensor([1.0, 2.0]))
+    opt = torch.optim.SGD([w], lr=0.5)
+    handle = AmpHandle()
+    loss = (w * torch.tensor([1.0, 3.0])).sum()
+    with handle.scale_loss(loss, opt) as scaled:
+        assert float(scaled) == float(loss) * 2.**16
+        scaled.backward()
+    assert torch.equal(w.grad, torch.tensor([1.0, 3.0]))        # unscaled in place
+    opt.step()
+    assert torch.equal(w.data, torch.tensor([0.5, 0.5]))
+    # overflow: the next step() is a one-shot no-op and the scale halves
+    opt.zero_grad()
+    loss = (w * torch.tensor([float("inf"), 1.0])).sum()
+    with handle.scale_loss(loss, opt) as scaled:
+        scaled.backward()
+    before = w.data.clone()
+    opt.step()
+    assert torch.equal(w.data, before)
+    assert handle._default_scaler.loss_scale() == 2.**15
+    w.grad = torch.tensor([1.0, 1.0])
+    opt.step()                                                   # the real step is back
+    assert torch.equal(w.data, before - 0.5)
+    # wrapped optimizer with two losses: gradients of loss 0 are set aside and added back
+    w2 = torch.nn.Parameter(torch.tensor([1.0, 1.0]))
+    wrapped = AmpHandle().wrap_optimizer(torch.optim.SGD([w2], lr=1.0), num_loss=2)
+    with wrapped.scale_loss((w2 * 2).sum()) as s0:
+        s0.backward()
+    with wrapped.scale_loss((w2 * 3).sum()) as s1:
+        s1.backward()
+    assert torch.equal(w2.grad, torch.tensor([5.0, 5.0]))
+    wrapped.step()
+    assert torch.equal(w2.data, torch.tensor([-4.0, -4.0]))
+    with pytest.raises(NotImplementedError):
+        wrapped.step(closure=lambda: None)
+    noop = NoOpHandle()
+    with noop.scale_loss(loss, opt) as same:
+        assert same is loss
+
+
+def test_fp16util_functions(golden_json, golden_arrays, cpu_backend):
+    from apex_b200 import fp16_utils as U
+    n = golden_json["fp16util"]["n_model"]
+    for flat in (False, True):
+        model = torch.nn.Sequential(torch.nn.Linear(8, 5), torch.nn.Linear(5, 3)).half()
+        for i, p in enumerate(model.parameters()):
+            p.data = tensor_from(golden_arrays["fp16util/%s/model/%d" % (flat, i)])
+        model_params, master_params = U.prep_param_lists(model, flat_master=flat)
+        assert len(master_params) == (1 if flat else n)
+        assert all(m.dtype == torch.float32 and m.requires_grad for m in master_params)
+        for i, p in enumerate(model_params):
+            p.grad = tensor_from(golden_arrays["fp16util/%s/grad/%d" % (flat, i)])
+        U.model_grads_to_master_grads(model_params, master_params, flat_master=flat)
+        for i, m in enumerate(master_params):
+            assert np.array_equal(m.grad.data.numpy(), golden_arrays["fp16util/%s/master_grad/%d" % (flat, i)])
+            m.data.copy_(tensor_from(golden_arrays["fp16util/%s/master_new/%d" % (flat, i)]))
+        U.master_params_to_model_params(model_params, master_params, flat_master=flat)
+        for i, p in enumerate(model_params):
+            assert np.array_equal(bits(p.data), golden_arrays["fp16util/%s/model_new/%d" % (flat, i)])
+    # a parameter without gradient clears the master's gradient (fp16util.py:111-112)
+    model_params, master_params = U.prep_param_lists(model)
+    master_params[0].grad = torch.zeros_like(master_params[0])
+    model_params[0].grad = None
+    U.model_grads_to_master_grads(model_params, master_params)
+    assert master_params[0].grad is None
+
+
+def test_network_to_half_keeps_batchnorm_fp32():
+    from apex_b200.fp16_utils import network_to_half, tofp16, BN_convert_float
+    net = torch.nn.Sequential(torch.nn.Linear(4, 4), torch.nn.BatchNorm1d(4))
+    half = network_to_half(net)
+    assert isinstance(half[0], tofp16)
+    assert half[1][0].weight.dtype == torch.float16 and half[1][1].weight.dtype == torch.float32
