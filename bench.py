@@ -1,0 +1,429 @@
+#!/usr/bin/env python
+"""bench.py -- the mixed-precision gradient step on B200, one JSON line.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 \
+        --master-port P bench.py --gpus N --steps K --warmup W
+
+Workload (BASELINE.json metric: "fused MP step ... (1.5B params)"): a GPT-2-XL-shaped set of
+580 fp16 parameter tensors (1,557,611,200 elements) with fp16 gradients, fp32 masters and fp32
+Adam state, all synthetic and resident in HBM.  One step = what the reference does between the
+end of backward and the next forward (apex/fp16_utils/fp16_optimizer.py:486-497, :330-384):
+inf/NaN check of every gradient feeding DynamicLossScaler, unscale into fp32, Adam update of the
+fp32 masters, copy back to the fp16 parameters -- driven through apex_b200.fp16_utils.FP16_Optimizer.
+With N > 1 each rank first averages its gradients with the other ranks bucket by bucket
+(apex/parallel/distributed.py:11-23: gather -> NCCL all_reduce -> x 1/N + scatter) on a side
+stream, exactly the calls DistributedDataParallel makes per bucket.
+
+`value` counts parameter elements updated per second over all ranks (weak scaling: every rank
+owns a full replica and its own gradients).
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ADAM = dict(lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0)
+BYTES_PER_PARAM_ADAM = 28        # r g16 2, r p32 4, r m 4, r v 4, w p32 4, w m 4, w v 4, w p16 2
+
+
+def gpt2_shapes(L, d, V=50257, T=1024):
+    per_layer = [(d,), (d,), (d, 3 * d), (3 * d,), (d, d), (d,), (d,), (d,), (d, 4 * d), (4 * d,), (4 * d, d), (d,)]
+    return [(V, d), (T, d)] + per_layer * L + [(d,), (d,)]
+
+
+def numel(shape):
+    n = 1
+    for s in shape:
+        n *= s
+    return n
+
+
+WORKLOADS = {
+    # name: (shapes, description)
+    "gpt2-xl": (gpt2_shapes(48, 1600), "GPT-2-XL-shaped 1.5B fp16 params, 580 tensors"),
+    "gpt2-medium": (gpt2_shapes(24, 1024), "GPT-2-medium-shaped 355M fp16 params, 292 tensors"),
+    "mlp": ([(4096, 1024), (4096,), (1024, 4096), (1024,)], "config-1 MLP, 8.4M fp16 params, 4 tensors"),
+}
+
+
+def measured_peak():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    try:
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    except Exception:       # noqa: BLE001
+        return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+class ClockSampler(object):
+    """nvidia-smi clocks and throttle reasons DURING the timed region."""
+    QUERY = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+             "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+             "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.proc = None
+        self.lines = []
+        self.thread = None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.QUERY,
+                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+        except Exception:   # noqa: BLE001
+            self.proc = None
+            return
+
+        def pump():
+            for line in self.proc.stdout:
+                self.lines.append(line.strip())
+        self.thread = threading.Thread(target=pump, daemon=True)
+        self.thread.start()
+
+    def stop(self):
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=5)
+        except Exception:   # noqa: BLE001
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for line in self.lines:
+            parts = [p.strip() for p in line.split(",")]
+            if len(parts) < 7:
+                continue
+            try:
+                sm.append(float(parts[0]))
+                mx.append(float(parts[1]))
+            except ValueError:
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "samples": len(sm), "reasons": sorted(reasons)}
+
+
+# ---------------------------------------------------------------------------------------------
+# the CPU arm: the oracle's restatement of the reference composition on host cores
+# ---------------------------------------------------------------------------------------------
+
+def cpu_reference_run(shapes, steps, warmup, budget_s, seed=1234):
+    """Time update_master_grads() + step() of the restated reference (oracle/apex_ref.py, which
+    calls torch.optim.Adam exactly where apex/fp16_utils/fp16_optimizer.py:380 does) on CPU
+    tensors, on a bounded sample of the workload.  Returns (params_per_s, info)."""
+    from oracle import apex_ref
+    # bounded sample: leading tensors of the workload up to ~40M elements (embedding excluded if too big)
+    sample, total = [], 0
+    for s in shapes[1:]:
+        if total + numel(s) > 40_000_000:
+            break
+        sample.append(s)
+        total += numel(s)
+    gen = torch.Generator().manual_seed(seed)
+    params = [torch.nn.Parameter((torch.randn(s, generator=gen) * 0.02).half()) for s in sample]
+    mp = apex_ref.MixedPrecisionStep(params, lambda ps: torch.optim.Adam(ps, **ADAM), dynamic_loss_scale=True,
+                                     dynamic_loss_args={"init_scale": 2.0**16})
+    grads = [(torch.randn(s, generator=gen) * (1e-3 * 65536)).half() for s in sample]
+    for p, g in zip(params, grads):
+        p.grad = g
+
+    def one():
+        mp.update_master_grads()
+        mp.step()
+    t_end = time.perf_counter() + budget_s
+    for _ in range(warmup):
+        one()
+        if time.perf_counter() > t_end:
+            break
+    times = []
+    t_end = time.perf_counter() + budget_s
+    for _ in range(steps):
+        t0 = time.perf_counter()
+        one()
+        times.append(time.perf_counter() - t0)
+        if time.perf_counter() > t_end and len(times) >= 3:
+            break
+    assert not mp.overflow
+    best = statistics.median(times)
+    info = {"sample": "first %d tensors after wte of the workload (%d params), %d timed steps, median"
+                      % (len(sample), total, len(times)),
+            "cores": torch.get_num_threads(), "host_cpus": os.cpu_count(), "ms_per_step": best * 1e3,
+            "params": total, "steps": len(times)}
+    return total / best, info
+
+
+def run_reference_arm(args, shapes):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return 0
+    value, info = cpu_reference_run(shapes, args.steps, args.warmup, budget_s=60.0)
+    line = {
+        "impl": "reference", "metric": "fused_mp_step_throughput", "value": value, "unit": "params/s",
+        "n_gpus": args.gpus, "steps": info["steps"], "warmup": args.warmup, "ms_per_step": info["ms_per_step"],
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][1] +
+                   "; dynamic-loss-scale check + unscale + Adam + fp16 copy", "optimizer": "Adam",
+                   "where": "host CPU, torch %s" % torch.__version__},
+        "cpu_baseline": {"value": value, "unit": "params/s", "cores": info["cores"], "kind": "port",
+                         "sample": info["sample"]},
+        "e2e": {"value": value, "unit": "params/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line))
+    return 0
+
+
+# ---------------------------------------------------------------------------------------------
+# our arm
+# ---------------------------------------------------------------------------------------------
+
+class Timed(object):
+    """CUDA-event timing of one python-level kernel wrapper, on the stream it launches on."""
+
+    def __init__(self, module, name):
+        self.module, self.name = module, name
+        self.real = getattr(module, name)
+        self.pairs = []
+        self.on = False
+        setattr(module, name, self)
+
+    def __call__(self, *a, **k):
+        if not self.on:
+            return self.real(*a, **k)
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        out = self.real(*a, **k)
+        e1.record()
+        self.pairs.append((e0, e1))
+        return out
+
+    def total_ms(self):
+        return sum(a.elapsed_time(b) for a, b in self.pairs)
+
+    def count(self):
+        return len(self.pairs)
+
+
+def build_buckets(params, bucket_elems):
+    """Bucket structure DistributedDataParallel learns when gradients arrive in reverse parameter
+    order (the usual order for a sequential model): apex/parallel/distributed.py:248-261, :176-180."""
+    from apex_b200.parallel.distributed import _BucketLayout, _DTYPE_CLASS
+    layout = _BucketLayout(bucket_elems)
+    for i in reversed(range(len(params))):
+        layout.arrive(_DTYPE_CLASS[params[i].dtype], i, params[i].numel())
+    layout.close()
+    return layout.members
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="gpt2-xl", choices=sorted(WORKLOADS))
+    ap.add_argument("--bucket-mb", type=float, default=256.0, help="DDP bucket size for N > 1 (fp16 bytes)")
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3)
+    shapes = WORKLOADS[args.workload][0]
+    n_params = sum(numel(s) for s in shapes)
+
+    if args.impl == "reference":
+        return run_reference_arm(args, shapes)
+
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the product path has no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    import torch.distributed as dist
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+
+    from apex_b200 import _C
+    from apex_b200.fp16_utils import FP16_Optimizer
+    from apex_b200.parallel.distributed import _FlatSlot, apply_flat_dist_call
+
+    gen = torch.Generator(device=dev).manual_seed(1234)            # identical replicas on every rank
+    params = [torch.nn.Parameter((torch.randn(s, generator=gen, device=dev) * 0.02).half()) for s in shapes]
+    opt = FP16_Optimizer(torch.optim.Adam(params, **ADAM), dynamic_loss_scale=True,
+                         dynamic_loss_args={"init_scale": 2.0**16, "scale_window": 1000}, verbose=False)
+    ggen = torch.Generator(device=dev).manual_seed(99 + rank)      # every rank has its own gradients
+    grads = [(torch.randn(s, generator=ggen, device=dev) * (1e-3 * 65536)).half() for s in shapes]
+    for p, g in zip(params, grads):
+        p.grad = g
+
+    side = torch.cuda.Stream()
+    buckets, slots = [], []
+    if world > 1:
+        bucket_elems = int(args.bucket_mb * (1 << 20) / 2)
+        buckets = [[grads[i] for i in b] for b in build_buckets(params, bucket_elems)]
+        slots = [_FlatSlot() for _ in buckets]
+        # what each rank started from, to restore between steps (averaging is not idempotent)
+    comm_events = []
+
+    def reduce_buckets():
+        """The per-bucket data path of DistributedDataParallel.comm_ready_buckets on its side stream."""
+        side.wait_stream(torch.cuda.current_stream())
+        with torch.cuda.stream(side):
+            e0 = torch.cuda.Event(enable_timing=True)
+            e1 = torch.cuda.Event(enable_timing=True)
+            e0.record()
+            for b, slot in zip(buckets, slots):
+                apply_flat_dist_call(b, dist.all_reduce, _slot=slot)
+            e1.record()
+            comm_events.append((e0, e1))
+        torch.cuda.current_stream().wait_stream(side)
+
+    def step():
+        if world > 1:
+            reduce_buckets()
+        opt.update_master_grads()
+        opt.step()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    t_check = Timed(_C, "mt_check_overflow")
+    t_fused = Timed(_C, "mt_fused_adam")
+
+    for _ in range(args.warmup):
+        step()
+    barrier()
+    assert opt.overflow is False, "synthetic gradients must not overflow in the timed region"
+
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)
+    t_check.on = t_fused.on = True
+    del comm_events[:]
+    launches0 = _C.launches
+    barrier()
+    start = torch.cuda.Event(enable_timing=True)
+    stop = torch.cuda.Event(enable_timing=True)
+    start.record()
+    for _ in range(args.steps):
+        step()
+    stop.record()
+    barrier()
+    elapsed_ms = start.elapsed_time(stop)
+    launches = _C.launches - launches0
+    t_check.on = t_fused.on = False
+    clocks = sampler.stop() if rank == 0 else None
+    if world > 1:
+        t = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        elapsed_ms = float(t.item())
+    ms_per_step = elapsed_ms / args.steps
+    value = world * n_params / (ms_per_step * 1e-3)
+
+    fused_ms = t_fused.total_ms() / max(t_fused.count(), 1)
+    check_ms = t_check.total_ms() / max(t_check.count(), 1)
+    comm_ms = sum(a.elapsed_time(b) for a, b in comm_events) / max(len(comm_events), 1) if comm_events else None
+    peak, peak_src = measured_peak()
+    achieved = BYTES_PER_PARAM_ADAM * n_params / (fused_ms * 1e-3) / 1e9
+    traffic = None
+    try:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            traffic = json.load(f).get(args.workload, {}).get("mt_fused_adam_kernel")
+    except Exception:   # noqa: BLE001
+        pass
+    roofline = {"bound": "hbm", "kernel": "mt_fused_adam_kernel", "achieved": achieved, "peak": peak,
+                "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
+                "algorithmic_bytes_per_launch": BYTES_PER_PARAM_ADAM * n_params, "avg_launch_ms": fused_ms,
+                "step_share": fused_ms / ms_per_step}
+
+    # ---- end to end through the public API, gradients arriving from pinned HOST memory ----------
+    e2e = None
+    if not args.no_e2e:
+        host = [torch.empty(g.shape, dtype=torch.float16).pin_memory() for g in grads]
+        for h, g in zip(host, grads):
+            h.copy_(g)
+        h2d = sum(h.numel() * 2 for h in host)
+
+        def e2e_step():
+            for p, h in zip(params, host):
+                p.grad.copy_(h, non_blocking=True)            # this step's inputs: host -> device
+            step()
+            return opt.overflow                               # the step's result: device -> host (4 bytes)
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        n_e2e = max(3, min(args.steps, 10))
+        t0 = time.perf_counter()
+        s0 = torch.cuda.Event(enable_timing=True)
+        s1 = torch.cuda.Event(enable_timing=True)
+        s0.record()
+        for _ in range(n_e2e):
+            e2e_step()
+        s1.record()
+        barrier()
+        e2e_ms = max(s0.elapsed_time(s1), (time.perf_counter() - t0) * 1e3) / n_e2e
+        if world > 1:
+            t = torch.tensor([e2e_ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            e2e_ms = float(t.item())
+        e2e = {"value": world * n_params / (e2e_ms * 1e-3), "unit": "params/s", "h2d_bytes_per_step": h2d,
+               "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms, "steps": n_e2e,
+               "api": "param.grad.copy_(pinned host) ; FP16_Optimizer.update_master_grads() ; .step() ; .overflow"}
+        del host
+
+    if rank == 0:
+        cpu = None
+        if world == 1 and not args.no_cpu_baseline:
+            v, info = cpu_reference_run(shapes, steps=10, warmup=2, budget_s=20.0)
+            cpu = {"value": v, "unit": "params/s", "cores": info["cores"], "kind": "port", "sample": info["sample"],
+                   "host_cpus": info["host_cpus"], "ms_per_step": info["ms_per_step"]}
+        line = {
+            "metric": "fused_mp_step_throughput", "value": value, "unit": "params/s", "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][1] +
+                       "; dynamic-loss-scale check + unscale + Adam + fp16 copy", "optimizer": "Adam",
+                       "params": n_params, "tensors": len(shapes), "parallelism": "dp%d" % world,
+                       "bucket_mb": args.bucket_mb if world > 1 else None, "buckets": len(buckets),
+                       "l2": "no flush needed: 24.9 GB of inputs per step >> 126 MB L2"
+                             if args.workload == "gpt2-xl" else "inputs larger than L2" },
+            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "breakdown_ms": {"check_overflow": check_ms, "fused_adam": fused_ms, "bucket_allreduce_path": comm_ms},
+            "hbm_gbs_step": (BYTES_PER_PARAM_ADAM + 2) * n_params / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
+        }
+        if comm_ms:
+            s_bytes = 2 * n_params
+            algbw = s_bytes / (comm_ms * 1e-3) / 1e9
+            line["allreduce"] = {"bytes": s_bytes, "ms": comm_ms, "algbw_gbs": algbw,
+                                 "busbw_gbs": algbw * 2 * (world - 1) / world, "nvlink_peak_gbs_per_dir": 900.0,
+                                 "frac_of_900": algbw * 2 * (world - 1) / world / 900.0,
+                                 "includes": "gather + NCCL all_reduce + x(1/N) scatter, per bucket, side stream"}
+        print(json.dumps(line))
+    if world > 1:
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())
