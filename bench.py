@@ -325,11 +325,13 @@ def main():
     barrier()
     start = torch.cuda.Event(enable_timing=True)
     stop = torch.cuda.Event(enable_timing=True)
+    torch.cuda.nvtx.range_push("apex_b200_timed")      # ncu --nvtx --nvtx-include "apex_b200_timed/"
     start.record()
     for _ in range(args.steps):
         step()
     stop.record()
     barrier()
+    torch.cuda.nvtx.range_pop()
     elapsed_ms = start.elapsed_time(stop)
     launches = _C.launches - launches0
     t_check.on = t_fused.on = False

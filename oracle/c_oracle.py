@@ -28,7 +28,7 @@ def lib():
         _lib.ora_sumsq_f16.restype = D
         _lib.ora_sumsq_f16.argtypes = [P, LL, D, I]
         _lib.ora_sumsq_f32.restype = D
-        _lib.ora_sumsq_f32.argtypes = [P, LL]
+        _lib.ora_sumsq_f32.argtypes = [P, LL, D, I]
     return _lib
 
 
@@ -112,5 +112,5 @@ def l2norm(grads, inv_scale=1.0, apply=False):
         if g.dtype == np.uint16:
             total += lib().ora_sumsq_f16(_p(g), g.size, float(inv_scale), int(apply))
         else:
-            total += lib().ora_sumsq_f32(_p(_c(g, np.float32)), g.size)
+            total += lib().ora_sumsq_f32(_p(_c(g, np.float32)), g.size, float(inv_scale), int(apply))
     return float(np.float32(np.sqrt(total)))

@@ -135,8 +135,8 @@ double ora_sumsq_f16(const uint16_t* g, long long n, double inv_scale, int apply
     for (long long i = 0; i < n; ++i) { float x = h2f(g[i]); if (apply) x = x * inv; acc += (double)x * (double)x; }
     return acc;
 }
-double ora_sumsq_f32(const float* g, long long n) {
-    double acc = 0.0;
-    for (long long i = 0; i < n; ++i) acc += (double)g[i] * (double)g[i];
+double ora_sumsq_f32(const float* g, long long n, double inv_scale, int apply) {
+    const float inv = (float)inv_scale; double acc = 0.0;
+    for (long long i = 0; i < n; ++i) { float x = g[i]; if (apply) x = x * inv; acc += (double)x * (double)x; }
     return acc;
 }
