@@ -77,6 +77,7 @@ SIGNATURES = {
     "apex_b200_mt_scale_unflatten": (_i, [_tp, _vp, _i, _i, _d, _i, _vp, _vp]),
     "apex_b200_scale_flat": (_i, [_vp, ctypes.c_int64, _i, _d, _vp, _vp]),
     "apex_b200_mt_l2norm": (_i, [_tp, _i, _d, _i, _vp, ctypes.c_int64, _vp, _vp]),
+    "apex_b200_mt_l2norm_noalloc": (_i, [_tp, _i, _d, _i, _vp, _vp]),
     "apex_b200_mt_clip_by_norm": (_i, [_tp, _i, _vp, _d, _vp, _vp]),
 }
 
@@ -232,6 +233,21 @@ def mt_l2norm(table, grad_list, inv_scale, apply_scale, partials, norm_out, stre
     _check(lib.apex_b200_mt_l2norm(table.ref, grad_list, float(inv_scale), int(bool(apply_scale)), _ptr(partials),
                                    0 if partials is None else partials.numel(), _ptr(norm_out),
                                    current_stream() if stream is None else stream), "mt_l2norm")
+
+
+NOALLOC_MAX_CHUNKS = 65536
+
+
+def mt_l2norm_noalloc(table, grad_list, inv_scale, apply_scale, norm_out, stream=None):
+    """apex_b200_mt_l2norm for callers that cannot allocate scratch (memory pool exhausted, or a
+    collective in flight that a cudaMalloc would stall): the partial sums use a fixed 256 KiB array
+    inside the library.  Tables with more than NOALLOC_MAX_CHUNKS chunks raise; calls on one GPU
+    must not overlap; make the first call on a device before any stream capture."""
+    global launches
+    launches += 2 if table.struct.total_chunks > 0 else 1
+    _check(lib.apex_b200_mt_l2norm_noalloc(table.ref, grad_list, float(inv_scale), int(bool(apply_scale)),
+                                           _ptr(norm_out), current_stream() if stream is None else stream),
+           "mt_l2norm_noalloc")
 
 
 def mt_clip_by_norm(table, grad_list, norm, max_norm, flag, stream=None):

@@ -7,6 +7,8 @@
 // goes to partials[chunk] -- caller-provided scratch.  Stage 2: one CTA adds the
 // partials in index order in fp64 and writes sqrt(total) as fp32.  The result
 // does not depend on the grid size or on scheduling.
+#include <atomic>
+
 #include "mt_common.cuh"
 
 namespace apex_b200 {
@@ -153,5 +155,72 @@ extern "C" int apex_b200_mt_clip_by_norm(const apex_b200_mt_table* t, int grad_l
     if (t->d_table == nullptr) return APEX_B200_EINVAL;
     mt_clip_kernel<<<mt_grid(t->total_chunks, 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         mt_view(t), grad_list, d_norm, static_cast<float>(max_norm), d_flag);
+    return mt_cuda_status();
+}
+
+// ---------------------------------------------------------------------------
+// The same norm for callers that must not allocate.
+//
+// apex_b200_mt_l2norm needs one float of scratch per chunk and expects the
+// caller to bring it.  Some callers cannot: a gradient-clipping call made while
+// the framework's memory pool is full (a job sized to fill the 180 GB) would
+// have to cudaMalloc, which can fail or make the pool flush and synchronise the
+// whole device; and code running on the autograd thread while the bucket
+// allreduce is still in flight on the reduction stream must not call
+// cudaMalloc/cudaFree either, because both wait for every stream of the device.
+// For them the partial sums live in a fixed array inside the library image.
+//
+// Cost and limits: APEX_B200_NOALLOC_MAX_CHUNKS floats (256 KiB) on every GPU
+// that loads the library, held until the process exits.  All calls on a device
+// share the array and it keeps the previous call's contents; each call writes
+// slots [0, total_chunks) before it reads them, so nothing has to start at
+// zero -- but two calls running at the same time on one GPU (two streams) would
+// overwrite each other's partial sums.  Serialise them.
+// ---------------------------------------------------------------------------
+
+static __device__ __align__(256) float g_norm_partials[APEX_B200_NOALLOC_MAX_CHUNKS];
+
+namespace {
+
+constexpr int kMaxDevices = 64;
+// Device address of g_norm_partials per device ordinal.  In host code the
+// symbol's name is only a handle; the address has to be asked for, once per
+// device, with that device current.
+std::atomic<float*> g_norm_partials_addr[kMaxDevices];
+
+int norm_partials_for_current_device(float** out) {
+    int dev = -1;
+    cudaError_t e = cudaGetDevice(&dev);
+    if (e != cudaSuccess) return int(e);
+    if (dev < 0 || dev >= kMaxDevices) return APEX_B200_ERANGE;
+    float* p = g_norm_partials_addr[dev].load(std::memory_order_acquire);
+    if (p == nullptr) {
+        void* sym = nullptr;
+        e = cudaGetSymbolAddress(&sym, g_norm_partials);
+        if (e != cudaSuccess) return int(e);
+        if (sym == nullptr) return APEX_B200_EINVAL;
+        p = static_cast<float*>(sym);
+        g_norm_partials_addr[dev].store(p, std::memory_order_release);   // racing threads store the same value
+    }
+    *out = p;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" int apex_b200_mt_l2norm_noalloc(const apex_b200_mt_table* t, int grad_list, double inv_scale,
+                                           int apply_scale, float* d_norm, void* stream) {
+    if (t == nullptr || d_norm == nullptr || grad_list < 0 || grad_list >= t->n_lists) return APEX_B200_EINVAL;
+    if (t->total_chunks < 0) return APEX_B200_EINVAL;
+    if (t->total_chunks > APEX_B200_NOALLOC_MAX_CHUNKS) return APEX_B200_ERANGE;   // does not fit the fixed array
+    if (t->total_chunks > 0 && t->d_table == nullptr) return APEX_B200_EINVAL;
+    float* partials = nullptr;
+    const int rc = norm_partials_for_current_device(&partials);    // first call on a device: set-up
+    if (rc != 0) return rc;
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    if (t->total_chunks > 0)
+        mt_sumsq_kernel<<<mt_grid(t->total_chunks, 8), kThreads, 0, s>>>(
+            mt_view(t), grad_list, static_cast<float>(inv_scale), apply_scale, partials);
+    norm_finish_kernel<<<1, kThreads, 0, s>>>(partials, t->total_chunks, d_norm);
     return mt_cuda_status();
 }

@@ -230,6 +230,26 @@ int apex_b200_mt_l2norm(const apex_b200_mt_table* t, int grad_list,
                         double inv_scale, int apply_scale, float* d_partials,
                         int64_t partials_len, float* d_norm, void* stream);
 
+/* No counterpart in the reference (it has no native code and lets torch allocate
+ * whatever it needs).  Same result as apex_b200_mt_l2norm, for callers that cannot
+ * allocate the `d_partials` scratch: a clip_master_grads issued while the
+ * framework's memory pool is exhausted (cudaMalloc may fail, or flush the pool and
+ * synchronise the device), or anything running while the bucket allreduce is still
+ * in flight on another stream (cudaMalloc/cudaFree wait for the whole device).
+ * The partial sums go to a fixed array of APEX_B200_NOALLOC_MAX_CHUNKS floats
+ * (256 KiB) that every GPU loading the library holds until exit; tables with more
+ * chunks are refused with APEX_B200_ERANGE.  This entry point calls no cudaMalloc,
+ * cudaFree or other allocating routine.  The first call on each device looks up
+ * the array's device address (once, with that device current); make that first
+ * call before starting any stream capture.  All calls on a device share the
+ * array, which keeps the last call's contents (every slot is written before it is
+ * read, nothing needs clearing): calls that overlap on the GPU race -- keep them
+ * on one stream or order them with events. */
+#define APEX_B200_NOALLOC_MAX_CHUNKS 65536
+int apex_b200_mt_l2norm_noalloc(const apex_b200_mt_table* t, int grad_list,
+                                double inv_scale, int apply_scale,
+                                float* d_norm, void* stream);
+
 /* Second half of clip_master_grads (apex/fp16_utils/fp16_optimizer.py:263):
  * in-place `g *= clip_coef` for fp32 gradients where
  * clip_coef = max_norm / (*d_norm + 1e-6), applied only when clip_coef < 1
