@@ -62,7 +62,8 @@ SIGNATURES = {
     "apex_b200_version": (_i, []),
     "apex_b200_error_string": (ctypes.c_char_p, [_i]),
     "apex_b200_device_info": (_i, [ctypes.POINTER(_i)] * 3),
-    "apex_b200_mt_table_bytes": (ctypes.c_size_t, [_i, _i]),
+    "apex_b200_mt_count_chunks": (ctypes.c_int64, [_i, _vp, _i]),
+    "apex_b200_mt_table_bytes": (ctypes.c_size_t, [_i, _i, ctypes.c_int64]),
     "apex_b200_mt_table_pack": (_i, [_vp, ctypes.c_size_t, _i, _i, _vp, _vp, _vp, _i, _tp]),
     "apex_b200_flag_clear": (_i, [_vp, _vp]),
     "apex_b200_mt_check_overflow": (_i, [_tp, _i, _vp, _vp]),
@@ -129,8 +130,15 @@ def _ptr(t):
     return None if t is None else t.data_ptr()
 
 
-def table_bytes(n_tensors, n_lists):
-    return lib.apex_b200_mt_table_bytes(n_tensors, n_lists)
+def count_chunks(n_tensors, numels_ptr, chunk_elems):
+    n = lib.apex_b200_mt_count_chunks(n_tensors, numels_ptr, chunk_elems)
+    if n < 0:
+        _check(int(n), "mt_count_chunks")
+    return int(n)
+
+
+def table_bytes(n_tensors, n_lists, total_chunks):
+    return lib.apex_b200_mt_table_bytes(n_tensors, n_lists, total_chunks)
 
 
 def table_pack(host_ptr, host_bytes, n_tensors, n_lists, numels_ptr, ptrs_ptr, flags_ptr, chunk_elems):

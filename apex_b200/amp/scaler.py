@@ -12,7 +12,7 @@ value, two launches instead of 3n.
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STREAM, new_flag
+from ..multi_tensor import TensorTable, CHUNK_ZERO, new_flag
 
 
 def _flags_for(grads):
@@ -40,7 +40,7 @@ class _Unscaler(object):
             return False
         dev = grads[0].device
         if self.table is None or self.table.device != dev:
-            self.table = TensorTable(dev, 1, CHUNK_STREAM)
+            self.table = TensorTable(dev, 1, CHUNK_ZERO)     # shared by the scan and the in-place unscale
             self.flag = new_flag(dev)
         self.table.update([grads], _flags_for(grads))
         _C.flag_clear(self.flag)

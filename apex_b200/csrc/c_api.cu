@@ -53,9 +53,19 @@ extern "C" int apex_b200_device_info(int* sm_count, int* cc_major, int* cc_minor
     return 0;
 }
 
-extern "C" size_t apex_b200_mt_table_bytes(int n_tensors, int n_lists) {
-    if (n_tensors < 0 || n_lists < 1) return 0;
-    return mt_total_bytes(n_tensors, n_lists);
+extern "C" int64_t apex_b200_mt_count_chunks(int n_tensors, const int64_t* numels, int chunk_elems) {
+    if (n_tensors < 0 || chunk_elems <= 0 || (n_tensors > 0 && numels == nullptr)) return APEX_B200_EINVAL;
+    int64_t chunks = 0;
+    for (int i = 0; i < n_tensors; ++i) {
+        if (numels[i] < 0) return APEX_B200_EINVAL;
+        chunks += (numels[i] + chunk_elems - 1) / chunk_elems;
+    }
+    return chunks;
+}
+
+extern "C" size_t apex_b200_mt_table_bytes(int n_tensors, int n_lists, int64_t total_chunks) {
+    if (n_tensors < 0 || n_lists < 1 || total_chunks < 0) return 0;
+    return mt_total_bytes(n_tensors, n_lists, total_chunks);
 }
 
 extern "C" int apex_b200_mt_table_pack(void* host_buf, size_t host_buf_bytes, int n_tensors, int n_lists,
@@ -64,7 +74,10 @@ extern "C" int apex_b200_mt_table_pack(void* host_buf, size_t host_buf_bytes, in
     if (host_buf == nullptr || out == nullptr || n_tensors < 0 || n_lists < 1) return APEX_B200_EINVAL;
     if (n_tensors > 0 && (numels == nullptr || ptrs == nullptr)) return APEX_B200_EINVAL;
     if (chunk_elems <= 0 || chunk_elems % kTile != 0) return APEX_B200_EINVAL;
-    const size_t need = mt_total_bytes(n_tensors, n_lists);
+    const int64_t want_chunks = apex_b200_mt_count_chunks(n_tensors, numels, chunk_elems);
+    if (want_chunks < 0) return APEX_B200_EINVAL;
+    if (want_chunks > 0x7fffffff) return APEX_B200_ERANGE;
+    const size_t need = mt_total_bytes(n_tensors, n_lists, want_chunks);
     if (host_buf_bytes < need) return APEX_B200_ENOSPC;
 
     char* b = static_cast<char*>(host_buf);
@@ -75,6 +88,7 @@ extern "C" int apex_b200_mt_table_pack(void* host_buf, size_t host_buf_bytes, in
     int64_t* t_ptr = reinterpret_cast<int64_t*>(b + mt_off_ptr(n_tensors));
     int32_t* t_flags = reinterpret_cast<int32_t*>(b + mt_off_flags(n_tensors, n_lists));
     int32_t* t_cstart = reinterpret_cast<int32_t*>(b + mt_off_chunk_start(n_tensors, n_lists));
+    int32_t* t_ctensor = reinterpret_cast<int32_t*>(b + mt_off_chunk_tensor(n_tensors, n_lists));
 
     int64_t elems = 0, chunks = 0;
     for (int i = 0; i < n_tensors; ++i) {
@@ -83,8 +97,9 @@ extern "C" int apex_b200_mt_table_pack(void* host_buf, size_t host_buf_bytes, in
         t_estart[i] = elems;
         t_cstart[i] = int32_t(chunks);
         elems += numels[i];
-        chunks += (numels[i] + chunk_elems - 1) / chunk_elems;
-        if (chunks > 0x7fffffff) return APEX_B200_ERANGE;
+        const int64_t mine = (numels[i] + chunk_elems - 1) / chunk_elems;
+        for (int64_t c = 0; c < mine; ++c) t_ctensor[chunks + c] = i;
+        chunks += mine;
         int32_t f = flags ? (flags[i] & ~APEX_B200_TF_UNALIGNED) : 0;
         for (int l = 0; l < n_lists; ++l) {
             const uint64_t p = ptrs[size_t(l) * n_tensors + i];

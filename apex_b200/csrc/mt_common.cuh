@@ -2,9 +2,13 @@
 //
 // One launch walks a device-resident table of tensors (see include/apex_b200.h
 // for the layout).  Work is cut into chunks of `chunk_elems` elements that
-// never straddle a tensor; a CTA finds the tensor of its chunk with a binary
-// search over the per-tensor chunk prefix (n+1 ints, L1/L2 resident), so the
-// table is O(#tensors) and is rebuilt only when a pointer changes.
+// never straddle a tensor, ONE CTA PER CHUNK: measured on B200, short-lived
+// CTAs that each move one 2048-element tile (one 8-element vector per thread)
+// reach 6.9 TB/s on the 8-stream Adam pass where persistent grid-stride CTAs
+// stall at 6.0 TB/s (tools/tune_step.cu; the resident CTAs drift out of phase
+// instead of all reading, then all writing).  A CTA finds its tensor with one
+// load from the chunk->tensor map; the table is rebuilt only when a pointer
+// changes.
 //
 // Memory access: every stream is read/written exactly once, so loads bypass L1
 // allocation and all fp32 streams move as 256-bit vectors (LDG.E.ENL2.256 /
@@ -33,6 +37,7 @@ struct MtView {
     const int64_t* ptr;         // [n_lists][n]
     const int32_t* flags;       // [n]
     const int32_t* chunk_start; // [n+1]
+    const int32_t* chunk_tensor; // [total_chunks]
     int n;
     int n_lists;
     int chunk_elems;
@@ -46,7 +51,8 @@ __host__ __device__ inline size_t mt_off_elem_start(int n) { return mt_off_numel
 __host__ __device__ inline size_t mt_off_ptr(int n) { return mt_off_elem_start(n) + size_t(n + 1) * 8; }
 __host__ __device__ inline size_t mt_off_flags(int n, int l) { return mt_off_ptr(n) + size_t(n) * l * 8; }
 __host__ __device__ inline size_t mt_off_chunk_start(int n, int l) { return mt_align8(mt_off_flags(n, l) + size_t(n) * 4); }
-__host__ __device__ inline size_t mt_total_bytes(int n, int l) { return mt_align8(mt_off_chunk_start(n, l) + size_t(n + 1) * 4); }
+__host__ __device__ inline size_t mt_off_chunk_tensor(int n, int l) { return mt_align8(mt_off_chunk_start(n, l) + size_t(n + 1) * 4); }
+__host__ __device__ inline size_t mt_total_bytes(int n, int l, long long chunks) { return mt_align8(mt_off_chunk_tensor(n, l) + size_t(chunks) * 4); }
 
 inline MtView mt_view(const apex_b200_mt_table* t) {
     const char* b = static_cast<const char*>(t->d_table);
@@ -60,6 +66,7 @@ inline MtView mt_view(const apex_b200_mt_table* t) {
     v.ptr = reinterpret_cast<const int64_t*>(b + mt_off_ptr(v.n));
     v.flags = reinterpret_cast<const int32_t*>(b + mt_off_flags(v.n, v.n_lists));
     v.chunk_start = reinterpret_cast<const int32_t*>(b + mt_off_chunk_start(v.n, v.n_lists));
+    v.chunk_tensor = reinterpret_cast<const int32_t*>(b + mt_off_chunk_tensor(v.n, v.n_lists));
     return v;
 }
 
@@ -72,21 +79,14 @@ struct MtChunk {
     int64_t numel;   // elements in the tensor
 };
 
-// Largest t with chunk_start[t] <= chunk.  Uniform across the CTA, so the
-// loads are broadcasts that hit L1 after the first CTA on the SM.
+// Uniform across the CTA: one load for the tensor index, then the per-tensor
+// fields in parallel (all L1/L2 resident after the first CTAs).
 __device__ __forceinline__ MtChunk mt_locate(const MtView& v, int chunk) {
-    int lo = 0, hi = v.n;  // answer in [lo, hi)
-    while (hi - lo > 1) {
-        int mid = (lo + hi) >> 1;
-        if (__ldg(v.chunk_start + mid) <= chunk) lo = mid; else hi = mid;
-    }
-    // skip zero-sized tensors that share the same chunk_start
-    // (chunk_start[lo] <= chunk < chunk_start[lo+1] holds for the last of them)
     MtChunk c;
-    c.tensor = lo;
-    c.flags = __ldg(v.flags + lo);
-    c.numel = __ldg(v.numel + lo);
-    c.offset = int64_t(chunk - __ldg(v.chunk_start + lo)) * v.chunk_elems;
+    c.tensor = __ldg(v.chunk_tensor + chunk);
+    c.flags = __ldg(v.flags + c.tensor);
+    c.numel = __ldg(v.numel + c.tensor);
+    c.offset = int64_t(chunk - __ldg(v.chunk_start + c.tensor)) * v.chunk_elems;
     int64_t left = c.numel - c.offset;
     c.len = left < v.chunk_elems ? int(left) : v.chunk_elems;
     return c;
@@ -175,12 +175,9 @@ __device__ __forceinline__ void mt_raise_flag(bool bad, int tensor, int32_t* fla
     if (block_bad && threadIdx.x == 0) atomicMax(flag, 0x7fffffff - tensor);
 }
 
-// Grid sizing: persistent CTAs, a whole number of them per SM.
+// Grid sizing: one CTA per chunk (see the header comment).
 int mt_sm_count();
-inline int mt_grid(int total_chunks, int ctas_per_sm) {
-    const long long cap = (long long)mt_sm_count() * ctas_per_sm;
-    return int(total_chunks < cap ? total_chunks : cap);
-}
+inline int mt_grid(int total_chunks, int /*unused*/) { return total_chunks; }
 
 inline int mt_cuda_status() {
     cudaError_t e = cudaPeekAtLastError();

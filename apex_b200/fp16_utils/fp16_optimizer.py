@@ -34,7 +34,7 @@ import weakref
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STEP, CHUNK_STREAM, new_flag
+from ..multi_tensor import TensorTable, CHUNK_STEP, CHUNK_STREAM, CHUNK_CHECK, CHUNK_ZERO, new_flag
 from .loss_scaler import DynamicLossScaler, LossScaler
 from .fp16util import master_params_to_model_params, clip_grad_norm
 
@@ -239,7 +239,7 @@ class FP16_Optimizer(object):
                 raise TypeError("apex_b200: unexpected gradient dtype %s" % g.dtype)
         self._ensure_device(grads[0])
         if self._zero_table is None:
-            self._zero_table = TensorTable(self._device, 1, CHUNK_STREAM)
+            self._zero_table = TensorTable(self._device, 1, CHUNK_ZERO)
         self._zero_table.update([grads], flags)
         _C.mt_zero(self._zero_table, 0, 2)
 
@@ -269,7 +269,7 @@ class FP16_Optimizer(object):
             return
         self._ensure_device(grads[0])
         if self._check_table is None:
-            self._check_table = TensorTable(self._device, 1, CHUNK_STREAM)
+            self._check_table = TensorTable(self._device, 1, CHUNK_CHECK)
         for g in grads:
             if not g.is_contiguous():
                 raise RuntimeError("apex_b200: gradients must be contiguous")

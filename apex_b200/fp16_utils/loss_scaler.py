@@ -9,7 +9,7 @@ launch that raises a single device word, and the host reads that word once.
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STREAM, new_flag
+from ..multi_tensor import TensorTable, CHUNK_CHECK, new_flag
 
 
 def to_python_float(t):
@@ -40,7 +40,7 @@ class _OverflowProbe(object):
         """Clear the flag and scan ``grads``; returns the device flag tensor (no sync)."""
         dev = grads[0].device
         if self.table is None or self.table.device != dev:
-            self.table = TensorTable(dev, 1, CHUNK_STREAM)
+            self.table = TensorTable(dev, 1, CHUNK_CHECK)
             self.flag = new_flag(dev)
         for g in grads:
             if not g.is_contiguous():

@@ -16,10 +16,20 @@ import torch
 
 from . import _C
 
-# Elements per chunk.  A chunk never straddles a tensor; a CTA processes one
-# chunk at a time with 256 threads x 8 elements per step.
-CHUNK_STEP = 16384      # fused update kernels (Adam: 448 KiB of traffic per chunk)
-CHUNK_STREAM = 65536    # pure streaming kernels (check / convert / flatten / zero)
+# Elements per chunk = per CTA (one CTA per chunk; a chunk never straddles a tensor).  Measured with
+# tools/kernel_bench.py on B200, GPT-2-XL shapes (GB/s of algorithmic bytes, torch copy_ = 6547):
+#   fused Adam   2048: 6850   4096: 6799   16384: 6647   65536: 6517     (persistent grid: 6000)
+#   fused SGD    2048: 6780   4096: 6822   16384: 6650
+#   check        2048: 2777   8192: 6887   16384: 7076   65536: 7126
+#   fp16<->fp32  2048: 4886   8192: 6022   16384: 6048   65536: 5832
+#   flatten      2048: 5687   8192: 6729   16384: 6629   65536: 6167
+#   zero         4096: 7050   16384: 7332  65536: 7141
+#   l2 norm      8192: 6234   16384: 6848  65536: 6980
+CHUNK_STEP = 2048       # fused update kernels: one 8-element vector per thread per CTA
+CHUNK_CHECK = 65536     # read-only overflow scan
+CHUNK_STREAM = 8192     # convert / copy / flatten / scatter / unscale
+CHUNK_ZERO = 16384
+CHUNK_NORM = 65536      # norm kernels: one fp32 partial sum per chunk
 
 
 class TensorTable(object):
@@ -70,7 +80,7 @@ class TensorTable(object):
         return True
 
     def _pack(self, n, ptrs, numels, fl):
-        nbytes = _C.table_bytes(n, self.n_lists)
+        nbytes = _C.table_bytes(n, self.n_lists, _C.count_chunks(n, numels.ctypes.data, self.chunk_elems))
         on_gpu = self.device.type == "cuda"
         if self._host is None or self._host.numel() < nbytes:
             cap = max(nbytes, 4096)

@@ -30,8 +30,9 @@
  *      int64  ptr[n_lists][n]           device addresses, list-major
  *      int32  flags[n]                  APEX_B200_TF_* bits per tensor
  *      int32  chunk_start[n+1]          exclusive prefix sum of ceil(numel/chunk_elems)
- *  A CTA maps its chunk id to (tensor, offset) by a binary search in
- *  chunk_start, so the table is O(n) however large the tensors are.
+ *      int32  chunk_tensor[total_chunks] tensor index of every chunk
+ *  Kernels launch ONE CTA PER CHUNK; a CTA maps its chunk id to (tensor, offset)
+ *  with one load from chunk_tensor.  (Every array starts 8-byte aligned.)
  */
 #ifndef APEX_B200_H_
 #define APEX_B200_H_
@@ -78,7 +79,12 @@ int apex_b200_device_info(int* sm_count, int* cc_major, int* cc_minor);
 
 /* ---- table packing (host only, no CUDA call) ---------------------------- */
 
-size_t apex_b200_mt_table_bytes(int n_tensors, int n_lists);
+/* Number of chunks a table over tensors of these sizes will have (>= 0), or a
+ * negative APEX_B200_E* code. */
+int64_t apex_b200_mt_count_chunks(int n_tensors, const int64_t* numels, int chunk_elems);
+
+/* Bytes of the packed table; total_chunks from apex_b200_mt_count_chunks. */
+size_t apex_b200_mt_table_bytes(int n_tensors, int n_lists, int64_t total_chunks);
 
 /* ptrs is list-major: ptrs[l * n_tensors + i].  flags may be NULL (all zero).
  * chunk_elems must be a positive multiple of 2048.  Tensors with numel == 0

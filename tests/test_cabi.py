@@ -24,7 +24,7 @@ def declared_symbols():
 
 def test_header_and_library_agree():
     declared = declared_symbols()
-    assert len(declared) >= 18
+    assert len(declared) >= 20
     out = subprocess.check_output(["nm", "-D", "--defined-only", _C.LIB_PATH]).decode()
     exported = sorted(set(re.findall(r"\bT (apex_b200_[a-z0-9_]+)", out)))
     assert exported == declared
@@ -41,7 +41,8 @@ def test_every_declaration_cites_the_reference():
     starts = sorted((text.rindex(" " + n + "("), n) for n in names)
     for k, (at, name) in enumerate(starts):
         if name in ("apex_b200_version", "apex_b200_error_string", "apex_b200_device_info",
-                    "apex_b200_mt_table_bytes", "apex_b200_mt_table_pack", "apex_b200_flag_clear"):
+                    "apex_b200_mt_count_chunks", "apex_b200_mt_table_bytes", "apex_b200_mt_table_pack",
+                    "apex_b200_flag_clear"):
             continue
         # everything between the previous declaration and this one (comment + any struct)
         comment = text[starts[k - 1][0]:at]
@@ -59,7 +60,8 @@ def test_version_and_error_strings():
 
 def _pack(numels, n_lists, ptrs, flags, chunk):
     n = len(numels)
-    nbytes = _C.table_bytes(n, n_lists)
+    arr = np.asarray(numels, np.int64)
+    nbytes = _C.table_bytes(n, n_lists, _C.count_chunks(n, arr.ctypes.data if n else None, chunk))
     buf = np.zeros(nbytes, np.uint8)
     st = _C.table_pack(buf.ctypes.data, nbytes, n, n_lists,
                        np.asarray(numels, np.int64).ctypes.data if n else None,
@@ -84,6 +86,9 @@ def test_table_pack_layout_ragged_and_empty():
     t_flags = np.frombuffer(buf, np.int32, n, off); off += 4 * n
     off = (off + 7) & ~7
     t_chunk = np.frombuffer(buf, np.int32, n + 1, off)
+    off = (off + 4 * (n + 1) + 7) & ~7
+    t_owner = np.frombuffer(buf, np.int32, st.total_chunks, off)
+    assert t_owner.tolist() == [0, 2, 2, 3, 5]                 # tensor of every chunk
     assert t_numel.tolist() == numels
     assert t_start.tolist() == [0, 5, 5, 5 + 16387, 5 + 16387 + 16384, 5 + 16387 + 16384, 5 + 16387 + 16384 + 1]
     assert t_ptr.tolist() == ptrs
