@@ -34,7 +34,8 @@ import weakref
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STEP, CHUNK_STREAM, CHUNK_CHECK, CHUNK_ZERO, new_flag
+from ..multi_tensor import (TensorTable, CHUNK_STEP, CHUNK_STREAM, CHUNK_CHECK, CHUNK_ZERO, new_flag,
+                            same_objects)
 from .loss_scaler import DynamicLossScaler, LossScaler
 from .fp16util import master_params_to_model_params, clip_grad_norm
 
@@ -77,6 +78,191 @@ class _MasterParam(torch.Tensor):
 def _raw_grad(t):
     """``t.grad`` without triggering materialisation."""
     return _tensor_grad.__get__(t)
+
+
+class _StepPlan(object):
+    """Everything one fused launch of one param group needs, remembered between steps.
+
+    Rebuilding it costs a python loop over every tensor (addresses, dtypes, state lookups); checking
+    that it is still valid costs identity comparisons only.  It is valid while the group still holds
+    the same parameter objects, the gradients are the same tensor objects, and optimizer.state still
+    holds the same state tensors.
+    """
+
+    def __init__(self):
+        self.kind = None
+        self.from_masters = False
+        self.owners = None       # keys of optimizer.state: masters then fp32-native params
+        self.group_params = None # the group's parameter list as it was when the plan was built
+        self.grads = None        # only used while building
+        self.table = None
+        self.state_tensors = None   # per owner: tuple of state tensors the kernel writes
+        self.state_keys = ()
+        self.fresh = None        # state created by us, published on the first committed step
+        self.steps = None        # adam: list of per-parameter step tensors
+        self.step_buf = None     # adam: the buffer our own step tensors are views of
+        self.momentum = 0.0
+        self.state_map = None
+        self.state_len = 0
+        self.state_dicts = None
+
+    @staticmethod
+    def build(opt, kind, gi, group, from_masters, halves, masters, floats, grads):
+        want16 = torch.float32 if from_masters else torch.float16
+        flag16 = (_C.TF_GRAD_F32 | _C.TF_NO_SCALE) if from_masters else 0
+        if len(halves) + len(floats) != len(group['params']):
+            return False          # param_groups edited behind our back
+        params, models, flags = [], [], []
+        n16 = len(halves)
+        for i, g in enumerate(grads):
+            want = want16 if i < n16 else torch.float32
+            if g is None or g.dtype != want or g.is_sparse or not g.is_contiguous():
+                return False
+        for model, master in zip(halves, masters):
+            params.append(master.data)
+            models.append(model.data)
+            flags.append(flag16)
+        for p in floats:
+            params.append(p.data)
+            models.append(None)
+            # already unscaled in place by update_master_grads, as the reference does
+            flags.append(_C.TF_GRAD_F32 | _C.TF_NO_MODEL | _C.TF_NO_SCALE)
+        for t in params + [m for m in models if m is not None]:
+            if not t.is_contiguous():
+                return False
+        opt._ensure_device(grads[0])
+        plan = _StepPlan()
+        plan.kind, plan.from_masters = kind, from_masters
+        plan.owners = list(masters) + list(floats)
+        plan.group_params = list(group['params'])
+        state = opt.optimizer.state
+        if kind == "sgd":
+            lists = plan._build_sgd(group, state, grads, params, models, flags)
+        else:
+            lists = plan._build_adam(state, grads, params, models, flags)
+        if lists is False:
+            return False
+        table = opt._step_tables.get(gi)
+        if table is None or table.n_lists != len(lists):
+            table = opt._step_tables[gi] = TensorTable(opt._device, len(lists), CHUNK_STEP)
+        table.update(lists, flags)
+        table.remember(grads)
+        plan.table = table
+        if not plan.fresh:
+            plan._bind_state(state)
+        return plan
+
+    def _build_sgd(self, group, state, grads, params, models, flags):
+        self.momentum = group['momentum']
+        bufs, fresh, held = [], [], []
+        if self.momentum != 0:
+            self.state_keys = ('momentum_buffer',)
+            for i, p in enumerate(self.owners):
+                buf = state[p].get('momentum_buffer') if p in state else None
+                if buf is None:
+                    # torch: buf = clone(grad) on the first step (sgd.py:361-362, :452-455)
+                    buf = torch.empty_like(params[i])
+                    fresh.append((p, {'momentum_buffer': buf}))
+                    flags[i] |= _C.TF_FIRST_STEP
+                elif buf.dtype != torch.float32 or not buf.is_contiguous():
+                    return False
+                bufs.append(buf)
+                held.append((buf,))
+        else:
+            bufs = [None] * len(self.owners)
+        self.fresh = fresh
+        self.state_tensors = held
+        return [grads, params, bufs, models]
+
+    def _build_adam(self, state, grads, params, models, flags):
+        self.state_keys = ('exp_avg', 'exp_avg_sq')
+        ms, vs, fresh, steps, held = [], [], [], [], []
+        missing = [p for p in self.owners if p not in state or len(state[p]) == 0]
+        if missing:
+            # torch's lazy state init (adam.py:_init_group).  Our step counters are views of one
+            # buffer so that a single add advances all of them.
+            step_dtype = torch.float64 if torch.get_default_dtype() == torch.float64 else torch.float32
+            self.step_buf = torch.zeros(len(missing), dtype=step_dtype)
+        k = 0
+        for i, p in enumerate(self.owners):
+            st = state[p] if p in state else {}
+            if len(st) == 0:
+                st = {'step': self.step_buf[k],
+                      'exp_avg': torch.zeros_like(params[i], memory_format=torch.preserve_format),
+                      'exp_avg_sq': torch.zeros_like(params[i], memory_format=torch.preserve_format)}
+                k += 1
+                fresh.append((p, st))
+            if not isinstance(st['step'], torch.Tensor) or st['step'].is_cuda:
+                return False
+            m, v = st['exp_avg'], st['exp_avg_sq']
+            if m.dtype != torch.float32 or v.dtype != torch.float32 or \
+                    not m.is_contiguous() or not v.is_contiguous():
+                return False
+            ms.append(m)
+            vs.append(v)
+            steps.append(st['step'])
+            held.append((m, v))
+        if len(set(float(s) for s in steps)) != 1:
+            return False          # per-tensor step counts differ: let torch handle it
+        self.fresh = fresh
+        self.steps = steps
+        self.state_tensors = held
+        return [grads, params, ms, vs, models]
+
+    def step_count(self):
+        return float(self.steps[0])
+
+    def _bind_state(self, state):
+        """Remember the state mapping and the per-parameter dicts (only once they all exist)."""
+        self.state_map = state
+        self.state_len = len(state)
+        self.state_dicts = [state[p] for p in self.owners] if self.state_keys else []
+
+    def still_valid(self, kind, from_masters, group, grads, state):
+        if kind != self.kind or from_masters != self.from_masters or self.fresh:
+            return False          # (a plan that still carries unpublished state is rebuilt)
+        if not same_objects(group['params'], self.group_params):
+            return False
+        if kind == "sgd" and group['momentum'] != self.momentum:
+            return False
+        if not self.table.built_from(grads):
+            return False
+        # optimizer state: torch replaces the whole mapping on load_state_dict; inside it, the
+        # per-parameter dicts we saw at build time must still hold the very same tensors
+        if state is not self.state_map or len(state) != self.state_len:
+            return False
+        keys = self.state_keys
+        if len(keys) == 1:
+            key = keys[0]
+            for st, held in zip(self.state_dicts, self.state_tensors):
+                if st.get(key) is not held[0]:
+                    return False
+        elif keys:
+            for st, held in zip(self.state_dicts, self.state_tensors):
+                for key, t in zip(keys, held):
+                    if st.get(key) is not t:
+                        return False
+        if self.steps is not None:
+            if self.state_dicts[0].get('step') is not self.steps[0] or \
+                    self.state_dicts[-1].get('step') is not self.steps[-1]:
+                return False
+        return True
+
+    def commit(self, state):
+        """The step was not skipped: publish state created for it and advance Adam's counters."""
+        fresh, self.fresh = self.fresh, []
+        for p, new in fresh:
+            state[p].update(new)
+        if self.state_keys and not fresh and self.state_dicts is None:
+            self._bind_state(state)
+        if self.steps is not None:
+            if self.step_buf is not None and len(self.steps) == self.step_buf.numel():
+                self.step_buf += 1
+            else:
+                torch._foreach_add_(self.steps, 1)
+        if fresh:
+            self.table.invalidate()       # the FIRST_STEP flags must go: rebuild next time
+            self.kind = None
 
 
 class FP16_Optimizer(object):
@@ -159,6 +345,7 @@ class FP16_Optimizer(object):
         self._unscale_table = None       # fp32-native gradients, unscaled in place
         self._grad_tables = {}           # group index -> table for materialisation
         self._step_tables = {}           # group index -> table for the fused step
+        self._plans = {}                 # group index -> cached _StepPlan
         self._zero_table = None
         self._norm_buf = None
 
@@ -247,35 +434,45 @@ class FP16_Optimizer(object):
 
     def _check_overflow(self):
         """Scan fp16 grads then fp32-native grads (reference order, :213-221); no host sync."""
-        grads, flags = [], []
-        for group in self.fp16_groups:
-            for param in group:
-                if param.grad is not None:
-                    grads.append(param.grad.data)
-                    flags.append(0)
-        for group in self.fp32_from_fp32_groups:
-            for param in group:
-                if param.grad is not None:
-                    grads.append(param.grad.data)
-                    flags.append(_C.TF_GRAD_F32)
         if not isinstance(self.loss_scaler, DynamicLossScaler):
             # a user-supplied scaler object: ask it, as the reference does
             params = [p for g in self.fp16_groups for p in g] + \
                      [p for g in self.fp32_from_fp32_groups for p in g]
             self.overflow = self.loss_scaler.has_overflow(params)
             return
+        grads = []
+        for group in self.fp16_groups:
+            for param in group:
+                g = param.grad
+                if g is not None:
+                    grads.append(g)
+        for group in self.fp32_from_fp32_groups:
+            for param in group:
+                g = param.grad
+                if g is not None:
+                    grads.append(g)
         if not grads:
             self.overflow = False
             return
         self._ensure_device(grads[0])
-        if self._check_table is None:
-            self._check_table = TensorTable(self._device, 1, CHUNK_CHECK)
-        for g in grads:
-            if not g.is_contiguous():
-                raise RuntimeError("apex_b200: gradients must be contiguous")
-        self._check_table.update([grads], flags)
+        table = self._check_table
+        if table is None:
+            table = self._check_table = TensorTable(self._device, 1, CHUNK_CHECK)
+        if not table.built_from(grads):
+            flags = []
+            for g in grads:
+                if not g.is_contiguous():
+                    raise RuntimeError("apex_b200: gradients must be contiguous")
+                if g.dtype == torch.float16:
+                    flags.append(0)
+                elif g.dtype == torch.float32:
+                    flags.append(_C.TF_GRAD_F32)
+                else:
+                    raise TypeError("apex_b200: unexpected gradient dtype %s" % g.dtype)
+            table.update([grads], flags)
+            table.remember(grads)
         _C.flag_clear(self._flag)
-        _C.mt_check_overflow(self._check_table, 0, self._flag)
+        _C.mt_check_overflow(table, 0, self._flag)
         self._flag_host.copy_(self._flag, non_blocking=True)
         ev = torch.cuda.Event()
         ev.record()
@@ -335,17 +532,23 @@ class FP16_Optimizer(object):
             for group in self.optimizer.param_groups:
                 for param in group['params']:
                     if param.grad is not None:
-                        grads.append(param.grad.data)
+                        grads.append(param.grad)
             self._unscale_in_place(grads, 1. / self.loss_scale, None)
 
     def _unscale_in_place(self, grads, inv_scale, flag):
         if not grads:
             return
         self._ensure_device(grads[0])
-        if self._unscale_table is None:
-            self._unscale_table = TensorTable(self._device, 1, CHUNK_STREAM)
-        self._unscale_table.update([grads], [_C.TF_GRAD_F32] * len(grads))
-        _C.mt_unscale(self._unscale_table, 0, inv_scale, flag, 0)
+        table = self._unscale_table
+        if table is None:
+            table = self._unscale_table = TensorTable(self._device, 1, CHUNK_STREAM)
+        if not table.built_from(grads):
+            for g in grads:
+                if g.dtype != torch.float32 or not g.is_contiguous():
+                    raise RuntimeError("apex_b200: fp32 gradients must be contiguous float tensors")
+            table.update([grads], [_C.TF_GRAD_F32] * len(grads))
+            table.remember(grads)
+        _C.mt_unscale(table, 0, inv_scale, flag, 0)
 
     # ---- clip ---------------------------------------------------------------------------
 
@@ -390,6 +593,7 @@ class FP16_Optimizer(object):
                 current.data.copy_(saved.data)
         for t in self._step_tables.values():
             t.invalidate()
+        self._plans = {}
 
     # ---- step -----------------------------------------------------------------------------------
 
@@ -475,141 +679,63 @@ class FP16_Optimizer(object):
         inv_scale, apply_scale = (1.0, False) if from_masters else pending
         plans = []
         for gi, group in enumerate(self.optimizer.param_groups):
-            plan = self._plan_group(kind, gi, group, from_masters)
+            plan = self._plan_for(kind, gi, group, from_masters)
             if plan is False:
                 return None
             if plan is not None:
-                plans.append(plan)
+                plans.append((group, plan))
         flag = self._live_flag()
-        commits = []
-        for gi, group, lists, flags, extra in plans:
-            table = self._step_tables.get(gi)
-            if table is None or table.n_lists != len(lists):
-                table = self._step_tables[gi] = TensorTable(self._device, len(lists), CHUNK_STEP)
-            table.update(lists, flags)
+        for group, plan in plans:
             if kind == "sgd":
-                _C.mt_fused_sgd(table, group['lr'], group['momentum'], group['dampening'],
+                _C.mt_fused_sgd(plan.table, group['lr'], group['momentum'], group['dampening'],
                                 group['weight_decay'], group['nesterov'], inv_scale, apply_scale, flag)
             else:
-                _C.mt_fused_adam(table, group['lr'], group['betas'][0], group['betas'][1], group['eps'],
-                                 group['weight_decay'], extra['step_size'], extra['bc2_sqrt'],
-                                 extra['decoupled'], inv_scale, apply_scale, flag)
-            commits.append(extra['commit'])
+                beta1, beta2 = group['betas']
+                step = plan.step_count() + 1
+                # torch/optim/adam.py:764-775, in python doubles
+                bias_correction1 = 1 - beta1 ** step
+                bias_correction2 = 1 - beta2 ** step
+                step_size = (group['lr'] / bias_correction1) * -1
+                _C.mt_fused_adam(plan.table, group['lr'], beta1, beta2, group['eps'], group['weight_decay'],
+                                 step_size, bias_correction2 ** 0.5,
+                                 bool(group.get('decoupled_weight_decay', False)), inv_scale, apply_scale, flag)
 
         def commit():
-            for c in commits:
-                c()
+            for _, plan in plans:
+                plan.commit(self.optimizer.state)
         return commit
 
-    def _plan_group(self, kind, gi, group, from_masters):
-        """Tensor lists for one param group; False = not fusable, None = nothing to do."""
+    def _plan_for(self, kind, gi, group, from_masters):
+        """The cached launch plan of one param group, rebuilt when anything it was built from has
+        been replaced.  False = this group cannot be fused, None = nothing to do."""
         if group.get('maximize', False) or group.get('differentiable', False):
             return False
         if isinstance(group['lr'], torch.Tensor):
             return False
+        if kind == "adam":
+            if group.get('amsgrad', False) or group.get('capturable', False):
+                return False
+            if isinstance(group['betas'][0], torch.Tensor) or isinstance(group['betas'][1], torch.Tensor):
+                return False
         halves = self.fp16_groups[gi]
         masters = self.fp32_from_fp16_groups[gi]
         floats = self.fp32_from_fp32_groups[gi]
-        if len(halves) + len(floats) != len(group['params']):
-            return False          # param_groups edited behind our back
-        grads, params, models, flags = [], [], [], []
-        for model, master in zip(halves, masters):
-            if from_masters:
-                g, want, fl = _raw_grad(master), torch.float32, _C.TF_GRAD_F32 | _C.TF_NO_SCALE
-            else:
-                g, want, fl = model.grad, torch.float16, 0
-            if g is None or g.dtype != want or g.is_sparse or not g.is_contiguous():
-                return False
-            grads.append(g.data)
-            params.append(master.data)
-            models.append(model.data)
-            flags.append(fl)
-        for p in floats:
-            g = p.grad
-            if g is None or g.dtype != torch.float32 or g.is_sparse or not g.is_contiguous():
-                return False
-            grads.append(g.data)
-            params.append(p.data)
-            models.append(None)
-            # already unscaled in place by update_master_grads, as the reference does
-            flags.append(_C.TF_GRAD_F32 | _C.TF_NO_MODEL | _C.TF_NO_SCALE)
+        if from_masters:
+            grads = [_raw_grad(m) for m in masters]
+        else:
+            grads = [h.grad for h in halves]
+        grads += [p.grad for p in floats]
         if not grads:
             return None
-        for t in params + [m for m in models if m is not None]:
-            if not t.is_contiguous():
-                return False
-        self._ensure_device(grads[0])
-        owners = masters + floats          # keys of optimizer.state
-        if kind == "sgd":
-            return self._plan_sgd(gi, group, owners, grads, params, models, flags)
-        return self._plan_adam(gi, group, owners, grads, params, models, flags)
-
-    def _plan_sgd(self, gi, group, owners, grads, params, models, flags):
-        state = self.optimizer.state
-        bufs, fresh = [], []
-        if group['momentum'] != 0:
-            for i, p in enumerate(owners):
-                buf = state[p].get('momentum_buffer') if p in state else None
-                if buf is None:
-                    # torch: buf = clone(grad) on the first step (sgd.py:361-362, :452-455)
-                    buf = torch.empty_like(params[i])
-                    fresh.append((p, buf))
-                    flags[i] |= _C.TF_FIRST_STEP
-                elif buf.dtype != torch.float32 or not buf.is_contiguous():
-                    return False
-                bufs.append(buf)
-        else:
-            bufs = [None] * len(owners)
-
-        def commit():
-            for p, buf in fresh:
-                state[p]['momentum_buffer'] = buf
-        return gi, group, [grads, params, bufs, models], flags, {'commit': commit}
-
-    def _plan_adam(self, gi, group, owners, grads, params, models, flags):
-        if group.get('amsgrad', False) or group.get('capturable', False):
+        plan = self._plans.get(gi)
+        if plan is not None and plan.still_valid(kind, from_masters, group, grads, self.optimizer.state):
+            return plan
+        plan = _StepPlan.build(self, kind, gi, group, from_masters, halves, masters, floats, grads)
+        if plan is False:
+            self._plans.pop(gi, None)
             return False
-        beta1, beta2 = group['betas']
-        if isinstance(beta1, torch.Tensor) or isinstance(beta2, torch.Tensor):
-            return False
-        state = self.optimizer.state
-        ms, vs, fresh, steps = [], [], [], []
-        for i, p in enumerate(owners):
-            st = state[p] if p in state else {}
-            if len(st) == 0:
-                # torch's lazy state init (adam.py:_init_group)
-                step_dtype = torch.float64 if torch.get_default_dtype() == torch.float64 else torch.float32
-                new = {'step': torch.tensor(0.0, dtype=step_dtype),
-                       'exp_avg': torch.zeros_like(params[i], memory_format=torch.preserve_format),
-                       'exp_avg_sq': torch.zeros_like(params[i], memory_format=torch.preserve_format)}
-                fresh.append((p, new))
-                st = new
-            if not isinstance(st['step'], torch.Tensor) or st['step'].is_cuda:
-                return False
-            m, v = st['exp_avg'], st['exp_avg_sq']
-            if m.dtype != torch.float32 or v.dtype != torch.float32 or \
-                    not m.is_contiguous() or not v.is_contiguous():
-                return False
-            ms.append(m)
-            vs.append(v)
-            steps.append(st['step'])
-        step_vals = set(float(s) for s in steps)
-        if len(step_vals) != 1:
-            return False          # per-tensor step counts differ: let torch handle it
-        step = step_vals.pop() + 1
-        # torch/optim/adam.py:764-775, in python doubles
-        bias_correction1 = 1 - beta1 ** step
-        bias_correction2 = 1 - beta2 ** step
-        step_size = (group['lr'] / bias_correction1) * -1
-        bc2_sqrt = bias_correction2 ** 0.5
-
-        def commit():
-            for p, new in fresh:
-                state[p].update(new)
-            torch._foreach_add_(steps, 1)
-        extra = {'step_size': step_size, 'bc2_sqrt': bc2_sqrt,
-                 'decoupled': bool(group.get('decoupled_weight_decay', False)), 'commit': commit}
-        return gi, group, [grads, params, ms, vs, models], flags, extra
+        self._plans[gi] = plan
+        return plan
 
     # ---- backward ---------------------------------------------------------------------------------------
 
@@ -637,7 +763,7 @@ class FP16_Optimizer(object):
             return          # overflow already known on the host (custom scaler path)
         # fp32-native parameters are the user's own tensors: unscale in place now.
         if apply_scale:
-            grads = [p.grad.data for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
+            grads = [p.grad for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
             self._unscale_in_place(grads, inv_scale, flag)
         self._pending = (inv_scale, apply_scale)
 
@@ -660,6 +786,7 @@ class FP16_Optimizer(object):
 
     def _set_state(self, value):
         self.optimizer.state = value
+        self._plans = {}
 
     state = property(_get_state, _set_state)
 

@@ -11,6 +11,9 @@ Ownership: torch owns every tensor; the table borrows raw addresses for the
 duration of the launches the caller enqueues right after ``update`` and never
 frees or retains them (SURVEY.md 8b "Ownership").
 """
+import operator
+import weakref
+
 import numpy as np
 import torch
 
@@ -50,6 +53,23 @@ class TensorTable(object):
         self.lists = None      # kept only when _C.keep_table_refs is set (CPU test doubles)
         self.flags = None
         self.rebuilds = 0
+        self._refs = None      # weak references to the tensors the table was built from
+
+    # Fast path for callers that run every training step: "are these still the very same tensor
+    # objects the table was built from?" costs a few tens of microseconds for hundreds of tensors,
+    # whereas update() fetches every address again.  Weak references: the table must not keep
+    # gradients alive that the user has dropped (zero_grad(set_to_none=True)).
+    def built_from(self, objs):
+        refs = self._refs
+        if refs is None or len(refs) != len(objs) or self._key is None:
+            return False
+        for r, o in zip(refs, objs):
+            if r() is not o:
+                return False
+        return True
+
+    def remember(self, objs):
+        self._refs = [weakref.ref(o) for o in objs]
 
     def update(self, lists, flags=None):
         """Point the table at ``lists`` (n_lists sequences of equal length).
@@ -101,6 +121,12 @@ class TensorTable(object):
 
     def invalidate(self):
         self._key = None
+        self._refs = None
+
+
+def same_objects(a, b):
+    """True when two equally long sequences hold identical objects position by position."""
+    return len(a) == len(b) and all(map(operator.is_, a, b))
 
 
 def new_flag(device):

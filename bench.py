@@ -34,7 +34,12 @@ if ROOT not in sys.path:
     sys.path.insert(0, ROOT)
 
 ADAM = dict(lr=1e-3, betas=(0.9, 0.999), eps=1e-8, weight_decay=0.0)
-BYTES_PER_PARAM_ADAM = 28        # r g16 2, r p32 4, r m 4, r v 4, w p32 4, w m 4, w v 4, w p16 2
+SGD = dict(lr=0.1, momentum=0.9, weight_decay=1e-4)
+# algorithmic bytes per parameter element of the fused update
+BYTES_PER_PARAM = {"adam": 28,   # r g16 2, r p32 4, r m 4, r v 4, w p32 4, w m 4, w v 4, w p16 2
+                   "sgd": 20}    # r g16 2, r p32 4, r mom 4, w p32 4, w mom 4, w p16 2
+FUSED_WRAPPER = {"adam": "mt_fused_adam", "sgd": "mt_fused_sgd"}
+FUSED_KERNEL = {"adam": "mt_fused_adam_kernel", "sgd": "mt_fused_sgd_kernel<true>"}
 
 
 def gpt2_shapes(L, d, V=50257, T=1024):
@@ -49,12 +54,31 @@ def numel(shape):
     return n
 
 
+def resnet50_shapes():
+    """(shape, is_fp32) of torchvision-style ResNet-50 after network_to_half: convs/fc fp16, BatchNorm fp32
+    (apex/fp16_utils/fp16util.py:21-41).  161 tensors, 25,557,032 parameters."""
+    out = [((64, 3, 7, 7), False), ((64,), True), ((64,), True)]
+    inplanes = 64
+    for planes, blocks, stride in ((64, 3, 1), (128, 4, 2), (256, 6, 2), (512, 3, 2)):
+        for b in range(blocks):
+            out += [((planes, inplanes, 1, 1), False), ((planes,), True), ((planes,), True),
+                    ((planes, planes, 3, 3), False), ((planes,), True), ((planes,), True),
+                    ((planes * 4, planes, 1, 1), False), ((planes * 4,), True), ((planes * 4,), True)]
+            if b == 0:
+                out += [((planes * 4, inplanes, 1, 1), False), ((planes * 4,), True), ((planes * 4,), True)]
+            inplanes = planes * 4
+    out += [((1000, 2048), False), ((1000,), False)]
+    return out
+
+
 WORKLOADS = {
-    # name: (shapes, description)
-    "gpt2-xl": (gpt2_shapes(48, 1600), "GPT-2-XL-shaped 1.5B fp16 params, 580 tensors"),
-    "gpt2-medium": (gpt2_shapes(24, 1024), "GPT-2-medium-shaped 355M fp16 params, 292 tensors"),
-    "mlp": ([(4096, 1024), (4096,), (1024, 4096), (1024,)], "config-1 MLP, 8.4M fp16 params, 4 tensors"),
+    # name: (shapes, description, default optimizer)
+    "gpt2-xl": (gpt2_shapes(48, 1600), "GPT-2-XL-shaped 1.5B fp16 params, 580 tensors", "adam"),
+    "gpt2-medium": (gpt2_shapes(24, 1024), "GPT-2-medium-shaped 355M fp16 params, 292 tensors", "sgd"),
+    "resnet50": ([s for s, _ in resnet50_shapes()], "ResNet-50 shapes, 25.6M params, 55 fp16 + 106 fp32 tensors", "sgd"),
+    "mlp": ([(4096, 1024), (4096,), (1024, 4096), (1024,)], "config-1 MLP, 8.4M fp16 params, 4 tensors", "sgd"),
 }
+FP32_MASK = {"resnet50": [f for _, f in resnet50_shapes()]}
 
 
 def measured_peak():
@@ -123,21 +147,27 @@ class ClockSampler(object):
 # the CPU arm: the oracle's restatement of the reference composition on host cores
 # ---------------------------------------------------------------------------------------------
 
-def cpu_reference_run(shapes, steps, warmup, budget_s, seed=1234):
+def make_optimizer(kind):
+    if kind == "adam":
+        return lambda ps: torch.optim.Adam(ps, **ADAM)
+    return lambda ps: torch.optim.SGD(ps, **SGD)
+
+
+def cpu_reference_run(shapes, steps, warmup, budget_s, seed=1234, kind="adam"):
     """Time update_master_grads() + step() of the restated reference (oracle/apex_ref.py, which
     calls torch.optim.Adam exactly where apex/fp16_utils/fp16_optimizer.py:380 does) on CPU
     tensors, on a bounded sample of the workload.  Returns (params_per_s, info)."""
     from oracle import apex_ref
     # bounded sample: leading tensors of the workload up to ~40M elements (embedding excluded if too big)
     sample, total = [], 0
-    for s in shapes[1:]:
+    for s in (shapes[1:] if numel(shapes[0]) > 40_000_000 else shapes):
         if total + numel(s) > 40_000_000:
             break
         sample.append(s)
         total += numel(s)
     gen = torch.Generator().manual_seed(seed)
     params = [torch.nn.Parameter((torch.randn(s, generator=gen) * 0.02).half()) for s in sample]
-    mp = apex_ref.MixedPrecisionStep(params, lambda ps: torch.optim.Adam(ps, **ADAM), dynamic_loss_scale=True,
+    mp = apex_ref.MixedPrecisionStep(params, make_optimizer(kind), dynamic_loss_scale=True,
                                      dynamic_loss_args={"init_scale": 2.0**16})
     grads = [(torch.randn(s, generator=gen) * (1e-3 * 65536)).half() for s in sample]
     for p, g in zip(params, grads):
@@ -172,14 +202,14 @@ def run_reference_arm(args, shapes):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
-    value, info = cpu_reference_run(shapes, args.steps, args.warmup, budget_s=60.0)
+    value, info = cpu_reference_run(shapes, args.steps, args.warmup, budget_s=60.0, kind=args.optimizer)
     line = {
         "impl": "reference", "metric": "fused_mp_step_throughput", "value": value, "unit": "params/s",
         "n_gpus": args.gpus, "steps": info["steps"], "warmup": args.warmup, "ms_per_step": info["ms_per_step"],
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][1] +
-                   "; dynamic-loss-scale check + unscale + Adam + fp16 copy", "optimizer": "Adam",
-                   "where": "host CPU, torch %s" % torch.__version__},
+                   "; dynamic-loss-scale check + unscale + %s + fp16 copy" % args.optimizer,
+                   "optimizer": args.optimizer, "where": "host CPU, torch %s" % torch.__version__},
         "cpu_baseline": {"value": value, "unit": "params/s", "cores": info["cores"], "kind": "port",
                          "sample": info["sample"]},
         "e2e": {"value": value, "unit": "params/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
@@ -239,12 +269,16 @@ def main():
     ap.add_argument("--warmup", type=int, default=5)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="gpt2-xl", choices=sorted(WORKLOADS))
+    ap.add_argument("--optimizer", default=None, choices=["adam", "sgd"])
     ap.add_argument("--bucket-mb", type=float, default=256.0, help="DDP bucket size for N > 1 (fp16 bytes)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     shapes = WORKLOADS[args.workload][0]
+    if args.optimizer is None:
+        args.optimizer = WORKLOADS[args.workload][2]
+    kind = args.optimizer
     n_params = sum(numel(s) for s in shapes)
 
     if args.impl == "reference":
@@ -266,11 +300,14 @@ def main():
     from apex_b200.parallel.distributed import _FlatSlot, apply_flat_dist_call
 
     gen = torch.Generator(device=dev).manual_seed(1234)            # identical replicas on every rank
-    params = [torch.nn.Parameter((torch.randn(s, generator=gen, device=dev) * 0.02).half()) for s in shapes]
-    opt = FP16_Optimizer(torch.optim.Adam(params, **ADAM), dynamic_loss_scale=True,
+    fp32_mask = FP32_MASK.get(args.workload, [False] * len(shapes))
+    params = [torch.nn.Parameter(torch.randn(s, generator=gen, device=dev) * 0.02 if f32 else
+                                 (torch.randn(s, generator=gen, device=dev) * 0.02).half())
+              for s, f32 in zip(shapes, fp32_mask)]
+    opt = FP16_Optimizer(make_optimizer(kind)(params), dynamic_loss_scale=True,
                          dynamic_loss_args={"init_scale": 2.0**16, "scale_window": 1000}, verbose=False)
     ggen = torch.Generator(device=dev).manual_seed(99 + rank)      # every rank has its own gradients
-    grads = [(torch.randn(s, generator=ggen, device=dev) * (1e-3 * 65536)).half() for s in shapes]
+    grads = [(torch.randn(s, generator=ggen, device=dev) * (1e-3 * 65536)).to(p.dtype) for s, p in zip(shapes, params)]
     for p, g in zip(params, grads):
         p.grad = g
 
@@ -296,11 +333,15 @@ def main():
             comm_events.append((e0, e1))
         torch.cuda.current_stream().wait_stream(side)
 
+    host_s = [0.0]
+
     def step():
+        t0 = time.perf_counter()
         if world > 1:
             reduce_buckets()
         opt.update_master_grads()
         opt.step()
+        host_s[0] += time.perf_counter() - t0
 
     def barrier():
         if world > 1:
@@ -308,7 +349,7 @@ def main():
         torch.cuda.synchronize()
 
     t_check = Timed(_C, "mt_check_overflow")
-    t_fused = Timed(_C, "mt_fused_adam")
+    t_fused = Timed(_C, FUSED_WRAPPER[kind])
 
     for _ in range(args.warmup):
         step()
@@ -321,6 +362,7 @@ def main():
         time.sleep(0.3)
     t_check.on = t_fused.on = True
     del comm_events[:]
+    host_s[0] = 0.0
     launches0 = _C.launches
     barrier()
     start = torch.cuda.Event(enable_timing=True)
@@ -333,6 +375,7 @@ def main():
     barrier()
     torch.cuda.nvtx.range_pop()
     elapsed_ms = start.elapsed_time(stop)
+    host_ms_per_step = host_s[0] / args.steps * 1e3      # python time inside step(), timed region only
     launches = _C.launches - launches0
     t_check.on = t_fused.on = False
     clocks = sampler.stop() if rank == 0 else None
@@ -347,25 +390,26 @@ def main():
     check_ms = t_check.total_ms() / max(t_check.count(), 1)
     comm_ms = sum(a.elapsed_time(b) for a, b in comm_events) / max(len(comm_events), 1) if comm_events else None
     peak, peak_src = measured_peak()
-    achieved = BYTES_PER_PARAM_ADAM * n_params / (fused_ms * 1e-3) / 1e9
+    bpp = BYTES_PER_PARAM[kind]
+    achieved = bpp * n_params / (fused_ms * 1e-3) / 1e9
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get(args.workload, {}).get("mt_fused_adam_kernel")
+            traffic = json.load(f).get(args.workload, {}).get(FUSED_KERNEL[kind])
     except Exception:   # noqa: BLE001
         pass
-    roofline = {"bound": "hbm", "kernel": "mt_fused_adam_kernel", "achieved": achieved, "peak": peak,
+    roofline = {"bound": "hbm", "kernel": FUSED_KERNEL[kind], "achieved": achieved, "peak": peak,
                 "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "peak_source": peak_src,
-                "algorithmic_bytes_per_launch": BYTES_PER_PARAM_ADAM * n_params, "avg_launch_ms": fused_ms,
+                "algorithmic_bytes_per_launch": bpp * n_params, "avg_launch_ms": fused_ms,
                 "step_share": fused_ms / ms_per_step}
 
     # ---- end to end through the public API, gradients arriving from pinned HOST memory ----------
     e2e = None
     if not args.no_e2e:
-        host = [torch.empty(g.shape, dtype=torch.float16).pin_memory() for g in grads]
+        host = [torch.empty(g.shape, dtype=g.dtype).pin_memory() for g in grads]
         for h, g in zip(host, grads):
             h.copy_(g)
-        h2d = sum(h.numel() * 2 for h in host)
+        h2d = sum(h.numel() * h.element_size() for h in host)
 
         def e2e_step():
             for p, h in zip(params, host):
@@ -397,7 +441,7 @@ def main():
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
-            v, info = cpu_reference_run(shapes, steps=10, warmup=2, budget_s=20.0)
+            v, info = cpu_reference_run(shapes, steps=10, warmup=2, budget_s=20.0, kind=kind)
             cpu = {"value": v, "unit": "params/s", "cores": info["cores"], "kind": "port", "sample": info["sample"],
                    "host_cpus": info["host_cpus"], "ms_per_step": info["ms_per_step"]}
         line = {
@@ -405,14 +449,14 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": args.workload + ": " + WORKLOADS[args.workload][1] +
-                       "; dynamic-loss-scale check + unscale + Adam + fp16 copy", "optimizer": "Adam",
+                       "; dynamic-loss-scale check + unscale + %s + fp16 copy" % kind, "optimizer": kind,
                        "params": n_params, "tensors": len(shapes), "parallelism": "dp%d" % world,
                        "bucket_mb": args.bucket_mb if world > 1 else None, "buckets": len(buckets),
-                       "l2": "no flush needed: 24.9 GB of inputs per step >> 126 MB L2"
-                             if args.workload == "gpt2-xl" else "inputs larger than L2" },
+                       "l2": "no flush: %.1f GB touched per step vs 126 MB L2" % ((bpp + 2) * n_params / 1e9)},
             "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
-            "breakdown_ms": {"check_overflow": check_ms, "fused_adam": fused_ms, "bucket_allreduce_path": comm_ms},
-            "hbm_gbs_step": (BYTES_PER_PARAM_ADAM + 2) * n_params / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
+            "breakdown_ms": {"check_overflow": check_ms, "fused_update": fused_ms, "bucket_allreduce_path": comm_ms,
+                             "host_python_per_step": host_ms_per_step},
+            "hbm_gbs_step": (bpp + 2) * n_params / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
         }
         if comm_ms:
             s_bytes = 2 * n_params
