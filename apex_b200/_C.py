@@ -77,6 +77,7 @@ SIGNATURES = {
     "apex_b200_mt_flatten": (_i, [_tp, _i, _vp, _i, _vp]),
     "apex_b200_mt_scale_unflatten": (_i, [_tp, _vp, _i, _i, _d, _i, _vp, _vp]),
     "apex_b200_scale_flat": (_i, [_vp, ctypes.c_int64, _i, _d, _vp, _vp]),
+    "apex_b200_symm_allreduce": (_i, [_vp, ctypes.c_uint64, _i, _i, ctypes.c_int64, _i, _i, _vp]),
     "apex_b200_mt_l2norm": (_i, [_tp, _i, _d, _i, _vp, ctypes.c_int64, _vp, _vp]),
     "apex_b200_mt_l2norm_noalloc": (_i, [_tp, _i, _d, _i, _vp, _vp]),
     "apex_b200_mt_clip_by_norm": (_i, [_tp, _i, _vp, _d, _vp, _vp]),
@@ -233,6 +234,15 @@ def scale_flat(flat, divisor, flag, stream=None):
         launches += 1
     _check(lib.apex_b200_scale_flat(_ptr(flat), flat.numel(), DTYPE_CODE[flat.dtype], float(divisor), _ptr(flag),
                                     current_stream() if stream is None else stream), "scale_flat")
+
+
+def symm_allreduce(peer_ptrs, multicast_ptr, rank, world, numel, dtype, ctas=0, stream=None):
+    """In-place SUM of a symmetric-memory buffer over `world` GPUs (this rank's half of the work)."""
+    global launches
+    launches += 1
+    arr = (ctypes.c_uint64 * len(peer_ptrs))(*peer_ptrs)
+    _check(lib.apex_b200_symm_allreduce(arr, int(multicast_ptr), rank, world, numel, DTYPE_CODE[dtype], ctas,
+                                        current_stream() if stream is None else stream), "symm_allreduce")
 
 
 def mt_l2norm(table, grad_list, inv_scale, apply_scale, partials, norm_out, stream=None):

@@ -26,6 +26,7 @@ from torch.nn.modules import Module
 
 from .. import _C
 from ..multi_tensor import TensorTable, CHUNK_STREAM
+from . import symm
 
 # bucket class per dtype; leftovers are appended in this order (reference :154-156, :178-180)
 _DTYPE_CLASS = {torch.float16: 0, torch.float32: 1, torch.float64: 2}
@@ -111,6 +112,74 @@ def apply_flat_dist_call(bucket, call, extra_args=None, _slot=None, _flag=None):
         _C.mt_scale_unflatten(slot.table, flat, 0, dist.get_world_size(), True, _flag)
     else:
         _C.mt_scale_unflatten(slot.table, flat, 0, 1.0, False, None)
+
+
+class _BucketPipeline(object):
+    """Averages buckets with the three stages of consecutive buckets overlapped:
+
+        gather stream :  gather(b+1)                 (apex_b200_mt_flatten)
+        NCCL stream   :        all_reduce(b)         (torch.distributed, async)
+        scatter stream:              x 1/world, scatter, check (b-1)   (apex_b200_mt_scale_unflatten)
+
+    The reference runs the three steps of a bucket back to back on one stream
+    (distributed.py:11-23 under :294-296), so HBM-bound copies and the NVLink-bound collective
+    never overlap.  The order of collectives is unchanged: buckets are issued in the order given.
+    """
+
+    def __init__(self, gather_stream):
+        self.gather_stream = gather_stream
+        self.scatter_stream = torch.cuda.Stream()
+        self.comm_stream = None        # only the symmetric-memory path needs its own collective stream
+        self.slots = {}
+
+    def reset(self):
+        self.slots = {}
+
+    def submit(self, key, bucket, flag=None):
+        """Enqueue the averaging of ``bucket``; returns at once.  Call from inside
+        ``with torch.cuda.stream(gather_stream)``."""
+        if len(bucket) == 0:
+            return
+        world = dist.get_world_size()
+        if len(bucket) == 1 and bucket[0].is_contiguous():
+            only = bucket[0]
+            work = dist.all_reduce(only, async_op=True)
+            with torch.cuda.stream(self.scatter_stream):
+                work.wait()
+                _C.scale_flat(only.view(-1), world, flag)
+            return
+        if symm.enabled() and bucket[0].dtype in (torch.float16, torch.float32):
+            # our own allreduce over peer-mapped memory instead of NCCL (parallel/symm.py)
+            slot = self.slots.get(key)
+            try:
+                if not isinstance(slot, symm.SymmSlot):
+                    slot = symm.SymmSlot()
+                    slot.bind(bucket)             # allocation + rendezvous: may not be possible on this box
+                    self.slots[key] = slot
+            except RuntimeError as err:           # every rank fails alike: the rendezvous is collective
+                symm.mark_broken(err)
+                self.slots.pop(key, None)
+            else:
+                if self.comm_stream is None:
+                    self.comm_stream = torch.cuda.Stream()
+                symm.average_bucket(slot, bucket, flag, self.comm_stream, self.scatter_stream)
+                return
+        slot = self.slots.get(key)
+        if not isinstance(slot, _FlatSlot):
+            slot = self.slots[key] = _FlatSlot()
+        flat = slot.bind(bucket)
+        _C.mt_flatten(slot.table, 0, flat)
+        work = dist.all_reduce(flat, async_op=True)
+        with torch.cuda.stream(self.scatter_stream):
+            work.wait()
+            _C.mt_scale_unflatten(slot.table, flat, 0, world, True, flag)
+
+    def join(self, stream):
+        """Make ``stream`` wait for everything submitted so far."""
+        stream.wait_stream(self.gather_stream)
+        if self.comm_stream is not None:
+            stream.wait_stream(self.comm_stream)
+        stream.wait_stream(self.scatter_stream)
 
 
 def flat_dist_call(tensors, call, extra_args=None):
@@ -310,7 +379,7 @@ class DistributedDataParallel(Module):
         self._round = None
         self._where = {}          # id(param) -> (bucket_idx, bucket_loc)
         self._index_of = {}       # id(param) -> index in active_params
-        self._slots = {}
+        self._pipeline = _BucketPipeline(self.reduction_stream)
 
         self.create_hooks()
         flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,))
@@ -343,14 +412,14 @@ class DistributedDataParallel(Module):
 
     def __getstate__(self):
         state = copy.copy(self.__dict__)
-        for transient in ("reduction_stream", "_slots", "_round"):
+        for transient in ("reduction_stream", "_pipeline", "_round"):
             state.pop(transient, None)
         return state
 
     def __setstate__(self, state):
         super(DistributedDataParallel, self).__setstate__(state)
         self.reduction_stream = torch.cuda.Stream()
-        self._slots = {}
+        self._pipeline = _BucketPipeline(self.reduction_stream)
         self._round = None
 
     # ---- structure ---------------------------------------------------------------------
@@ -364,7 +433,7 @@ class DistributedDataParallel(Module):
         dist.broadcast(info, 0)
         self._layout.decode(info.tolist())      # one device-to-host copy for the whole vector
         self._where = {id(self.active_params[i]): pos for i, pos in self._layout.positions().items()}
-        self._slots = {}
+        self._pipeline.reset()
 
     # ---- hooks ---------------------------------------------------------------------------
 
@@ -410,7 +479,7 @@ class DistributedDataParallel(Module):
 
     def _finish_backward_overlapped(self):
         """reference ``overlapping_backward_epilogue``: :223-233"""
-        torch.cuda.current_stream().wait_stream(self.reduction_stream)
+        self._pipeline.join(torch.cuda.current_stream())
         self._round.verify_complete()
 
     def comm_ready_buckets(self, param):
@@ -424,10 +493,7 @@ class DistributedDataParallel(Module):
         self.reduction_stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.reduction_stream):
             for b in eligible:
-                slot = self._slots.get(b)
-                if slot is None:
-                    slot = self._slots[b] = _FlatSlot()
-                apply_flat_dist_call(self._round.grads[b], dist.all_reduce, _slot=slot)
+                self._pipeline.submit(b, self._round.grads[b])
 
     # ---- forward -----------------------------------------------------------------------------
 

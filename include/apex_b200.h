@@ -222,6 +222,22 @@ int apex_b200_mt_scale_unflatten(const apex_b200_mt_table* t, const void* flat,
 int apex_b200_scale_flat(void* flat, int64_t numel, int dtype, double divisor,
                          int32_t* d_flag, void* stream);
 
+/* Replaces `dist.all_reduce(coalesced)` of apply_flat_dist_call
+ * (apex/parallel/distributed.py:15-17) for a flat bucket that lives in peer-mapped
+ * ("symmetric") memory of one NVLink domain: in-place SUM over `world` GPUs, two-shot,
+ * rank r reducing slice r and writing it to every copy.  With `multicast_ptr != 0`
+ * the NVSwitch does both halves (multimem.ld_reduce / multimem.st); otherwise
+ * `peer_ptrs[world]` (host array of the buffer's address on every rank, own rank
+ * included) is used with plain loads/stores over NVLink.  fp16 (dtype 0) is summed in
+ * fp32 and rounded once; fp32 is dtype 1.  numel must be a multiple of
+ * (16 / element size) * world (pad the buffer).  The call only launches this rank's
+ * kernel; the caller must order it after every rank has filled its buffer and must
+ * not read the result before every rank's kernel has finished (a cross-rank barrier
+ * on the stream before and after).  ctas <= 0 picks a default. */
+int apex_b200_symm_allreduce(const uint64_t* peer_ptrs, uint64_t multicast_ptr,
+                             int rank, int world, int64_t numel, int dtype,
+                             int ctas, void* stream);
+
 /* ---- gradient norm (clip_master_grads) ---------------------------------- */
 
 /* Replaces torch.nn.utils.clip_grad_norm_ as called by

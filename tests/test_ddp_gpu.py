@@ -84,9 +84,10 @@ def _worker(rank, world, port, out_dir):
     os.environ["MASTER_PORT"] = str(port)
     torch.cuda.set_device(rank)
     dist.init_process_group("nccl", rank=rank, world_size=world)
-    from apex_b200.parallel import DistributedDataParallel as DDP
+    from apex_b200.parallel import DistributedDataParallel as DDP, symm as _symm
     from apex_b200.parallel.distributed import flat_dist_call
     ok = {}
+    ok["symm_default_on"] = _symm.enabled()
 
     # the reference's known-answer test, verbatim sizes (tests/distributed/ddp_race_condition_test.py)
     class Model(torch.nn.Module):
@@ -105,7 +106,7 @@ def _worker(rank, world, port, out_dir):
         model.zero_grad()
         model(x).sum().backward()
         for param, val in ((model.module.a, 2.), (model.module.b, 1.)):
-            expected = val * 4096 * 4096 * (2. * i + 1) / 2.
+            expected = val * 4096 * 4096 * (2. * i + (world - 1)) / 2.      # world = 2: the reference's formula
             passed &= (param.grad.data.sum().item() == expected)
     ok["race"] = bool(passed)
 
@@ -115,22 +116,75 @@ def _worker(rank, world, port, out_dir):
     exact = [t.float() for t in tensors]
     for e in exact:
         dist.all_reduce(e)
+    # what the reference itself computes: cat, NCCL all_reduce in fp16, /= world (distributed.py:12-20)
+    ref = torch.cat([t.view(-1) for t in tensors])
+    dist.all_reduce(ref)
+    ref /= world
     flat_dist_call(tensors, dist.all_reduce)
     torch.cuda.synchronize()
-    close = all(torch.allclose(t.float(), e / world, rtol=1e-3, atol=1e-2) for t, e in zip(tensors, exact))
+    mine = torch.cat([t.view(-1) for t in tensors])
+    close = torch.allclose(mine.float(), ref.float(), rtol=1e-3, atol=1e-3)     # north_star: rtol 1e-3 for fp16 sums
+    ok["fp16_same_bits_as_reference_composition"] = bool(torch.equal(mine, ref))
+    # and not far from the true mean (fp16 partial sums round at every hop of NCCL's ring)
+    close &= all(torch.allclose(t.float(), e / world, rtol=5e-3, atol=0.3) for t, e in zip(tensors, exact))
     ok["fp16_average"] = bool(close)
     big = torch.full((1000,), 40000.0, device="cuda").half()
     flat_dist_call([big, big.clone()], dist.all_reduce)
     ok["fp16_overflow_stays_inf"] = bool(torch.isinf(big).all())
+    # our own allreduce over symmetric memory (switch multicast if the box has it, and peer-to-peer)
+    from apex_b200.parallel import symm
+    from apex_b200.parallel.distributed import _BucketPipeline
+    symm.enable(True)
+    for mode, force_p2p in (("symm_auto", False), ("symm_p2p", True)):
+        symm._force_p2p = force_p2p
+        symm._force_mc = not force_p2p
+        pipe = _BucketPipeline(torch.cuda.current_stream())
+        g = torch.Generator(device="cuda").manual_seed(50 + rank)
+        t16 = [(torch.randn(n, generator=g, device="cuda") * 100).half() for n in (5, 4099, 1 << 20, 33, 70001)]
+        t32 = [torch.randn(n, generator=g, device="cuda") * 100 for n in (7, 65536, 12345)]
+        e16 = [t.float() for t in t16]
+        e32 = [t.clone() for t in t32]
+        for e in e16 + e32:
+            dist.all_reduce(e)
+        flag = torch.zeros(1, dtype=torch.int32, device="cuda")
+        for it in range(3):           # the buffers are reused: run it more than once
+            w16 = [t.clone() for t in t16]
+            w32 = [t.clone() for t in t32]
+            pipe.submit(0, w16, flag)
+            pipe.submit(1, w32, flag)
+            pipe.join(torch.cuda.current_stream())
+            torch.cuda.synchronize()
+            good = all(torch.allclose(t.float(), e / world, rtol=1e-3, atol=1e-2) for t, e in zip(w16, e16))
+            good &= all(torch.allclose(t, e / world, rtol=1e-5, atol=1e-4) for t, e in zip(w32, e32))
+            # every rank must hold identical bits
+            mine = torch.cat([t.view(-1).float() for t in w16 + w32])
+            other = mine.clone()
+            dist.broadcast(other, 0)
+            good &= bool(torch.equal(mine, other))
+            ok[mode] = ok.get(mode, True) and bool(good) and int(flag.item()) == 0
+        big = [torch.full((1000,), 40000.0, device="cuda").half(), torch.full((8,), 1.0, device="cuda").half()]
+        pipe.submit(2, big, flag)
+        pipe.join(torch.cuda.current_stream())
+        torch.cuda.synchronize()
+        ok[mode + "_overflow"] = bool(torch.isinf(big[0]).all()) and int(flag.item()) != 0
+        ok[mode + "_multicast"] = bool(pipe.slots[0].handle.multicast_ptr) and not force_p2p
+    symm._force_p2p = symm._force_mc = False
     torch.save(ok, os.path.join(out_dir, "rank%d.pt" % rank))
     dist.barrier()
     dist.destroy_process_group()
 
 
-@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs 2 GPUs")
+WORLD = int(os.environ.get("APEX_B200_TEST_WORLD", "2"))     # set to 4 or 8 on a bigger box
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < max(2, WORLD), reason="needs %d GPUs" % max(2, WORLD))
 def test_two_ranks_nccl(tmp_path):
     port = _free_port()
-    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
-    for r in range(2):
+    mp.spawn(_worker, args=(WORLD, port, str(tmp_path)), nprocs=WORLD, join=True)
+    for r in range(WORLD):
         res = torch.load(os.path.join(str(tmp_path), "rank%d.pt" % r), weights_only=False)
-        assert res == {"race": True, "fp16_average": True, "fp16_overflow_stays_inf": True}, res
+        for key in ("race", "fp16_average", "fp16_overflow_stays_inf", "symm_auto", "symm_p2p",
+                    "symm_auto_overflow", "symm_p2p_overflow"):
+            assert res[key] is True, (key, res)
+        print("multicast used:", res["symm_auto_multicast"], "| bits equal to reference composition:",
+              res["fp16_same_bits_as_reference_composition"], "| symm default:", res["symm_default_on"])
