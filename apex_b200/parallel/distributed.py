@@ -129,7 +129,7 @@ class _BucketPipeline(object):
     def __init__(self, gather_stream):
         self.gather_stream = gather_stream
         self.scatter_stream = torch.cuda.Stream()
-        self.comm_stream = None        # only the symmetric-memory path needs its own collective stream
+        self.symm_pipe = None          # created when the symmetric-memory path is first used
         self.slots = {}
 
     def reset(self):
@@ -160,9 +160,9 @@ class _BucketPipeline(object):
                 symm.mark_broken(err)
                 self.slots.pop(key, None)
             else:
-                if self.comm_stream is None:
-                    self.comm_stream = torch.cuda.Stream()
-                symm.average_bucket(slot, bucket, flag, self.comm_stream, self.scatter_stream)
+                if self.symm_pipe is None:
+                    self.symm_pipe = symm.SymmPipeline(self.gather_stream, self.scatter_stream)
+                self.symm_pipe.submit(slot, bucket, flag)
                 return
         slot = self.slots.get(key)
         if not isinstance(slot, _FlatSlot):
@@ -177,8 +177,8 @@ class _BucketPipeline(object):
     def join(self, stream):
         """Make ``stream`` wait for everything submitted so far."""
         stream.wait_stream(self.gather_stream)
-        if self.comm_stream is not None:
-            stream.wait_stream(self.comm_stream)
+        if self.symm_pipe is not None:
+            self.symm_pipe.join(stream)
         stream.wait_stream(self.scatter_stream)
 
 

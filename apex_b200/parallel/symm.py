@@ -84,15 +84,67 @@ class SymmSlot(object):
         self.table.update([tensors])
         return self.view
 
-    def allreduce(self):
+    def barrier(self, channel=0):
+        self.handle.barrier(channel=channel, timeout_ms=20000)
+
+    def launch_allreduce(self):
+        """This rank's half of the two-shot SUM; the caller provides the barriers."""
         h = self.handle
         mc = int(h.multicast_ptr or 0)
         use_mc = mc != 0 and not _force_p2p and (_force_mc or h.world_size > 2)
-        ctas = _ctas if _ctas > 0 else (64 if use_mc else 148)
-        h.barrier(channel=0, timeout_ms=20000)
+        ctas = _ctas if _ctas > 0 else (32 if use_mc else 148)
         _C.symm_allreduce(list(h.buffer_ptrs), mc if use_mc else 0, h.rank, h.world_size, self.flat.numel(),
                           self.flat.dtype, ctas)
-        h.barrier(channel=1, timeout_ms=20000)
+
+    def allreduce(self):
+        self.barrier(0)
+        self.launch_allreduce()
+        self.barrier(1)
+
+
+class SymmPipeline(object):
+    """gather / allreduce / scatter of consecutive buckets on three streams with ONE cross-rank
+    barrier per bucket: the barrier that tells rank r "every rank has gathered bucket b" is enqueued
+    by every rank after its allreduce of bucket b-1, so it also tells "bucket b-1 is complete
+    everywhere" and releases the scatter of b-1.  ``flush`` adds the barrier for the last bucket."""
+
+    def __init__(self, gather_stream, scatter_stream):
+        self.gather_stream = gather_stream
+        self.scatter_stream = scatter_stream
+        self.comm_stream = torch.cuda.Stream()
+        self.waiting = None          # (slot, view, flag) whose allreduce is enqueued but not yet certified
+
+    def _release(self, slot_for_barrier):
+        """On the comm stream: barrier, then let the scatter of the waiting bucket go."""
+        slot_for_barrier.barrier(0)
+        if self.waiting is not None:
+            slot, view, flag = self.waiting
+            self.waiting = None
+            done = torch.cuda.Event()
+            done.record()
+            with torch.cuda.stream(self.scatter_stream):
+                self.scatter_stream.wait_event(done)
+                _C.mt_scale_unflatten(slot.table, view, 0, dist.get_world_size(), True, flag)
+
+    def submit(self, slot, bucket, flag):
+        view = slot.bind(bucket)
+        _C.mt_flatten(slot.table, 0, view)            # on the gather stream (current)
+        gathered = torch.cuda.Event()
+        gathered.record()
+        with torch.cuda.stream(self.comm_stream):
+            self.comm_stream.wait_event(gathered)
+            self._release(slot)
+            slot.launch_allreduce()
+            self.waiting = (slot, view, flag)
+
+    def flush(self):
+        if self.waiting is not None:
+            with torch.cuda.stream(self.comm_stream):
+                self._release(self.waiting[0])
+
+    def join(self, stream):
+        self.flush()
+        stream.wait_stream(self.comm_stream)
 
 
 def average_bucket(slot, bucket, flag=None, comm_stream=None, scatter_stream=None):

@@ -20,6 +20,11 @@ PY
     echo "$TAG FAILED"; tail -5 gpurun_out/sweep_last.err
   fi
 }
+if [ "$QUICK" = "3" ]; then
+  TAG=auto run 256; TAG=auto run 1024; TAG=auto run 64
+  APEX_B200_SYMM_CTAS=64 TAG=auto_ctas64 run 256
+  exit 0
+fi
 if [ "$QUICK" = "2" ]; then
   APEX_B200_SYMM=0 TAG=nccl run 256
   APEX_B200_SYMM_P2P=0 TAG=nvls run 256
