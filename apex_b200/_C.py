@@ -41,7 +41,7 @@ class SgdArgs(ctypes.Structure):
     _fields_ = [("lr", ctypes.c_double), ("momentum", ctypes.c_double),
                 ("dampening", ctypes.c_double), ("weight_decay", ctypes.c_double),
                 ("nesterov", ctypes.c_int32), ("apply_scale", ctypes.c_int32),
-                ("inv_scale", ctypes.c_double)]
+                ("inv_scale", ctypes.c_double), ("clip_norm", ctypes.c_void_p), ("clip_max_norm", ctypes.c_double)]
 
 
 class AdamArgs(ctypes.Structure):
@@ -49,7 +49,7 @@ class AdamArgs(ctypes.Structure):
                 ("eps", ctypes.c_double), ("weight_decay", ctypes.c_double),
                 ("step_size", ctypes.c_double), ("bias_correction2_sqrt", ctypes.c_double),
                 ("decoupled_weight_decay", ctypes.c_int32), ("apply_scale", ctypes.c_int32),
-                ("inv_scale", ctypes.c_double)]
+                ("inv_scale", ctypes.c_double), ("clip_norm", ctypes.c_void_p), ("clip_max_norm", ctypes.c_double)]
 
 
 _vp = ctypes.c_void_p
@@ -68,7 +68,7 @@ SIGNATURES = {
     "apex_b200_flag_clear": (_i, [_vp, _vp]),
     "apex_b200_mt_check_overflow": (_i, [_tp, _i, _vp, _vp]),
     "apex_b200_mt_unscale": (_i, [_tp, _i, _d, _vp, _i, _vp]),
-    "apex_b200_mt_grads_to_master": (_i, [_tp, _i, _i, _d, _i, _vp, _vp]),
+    "apex_b200_mt_grads_to_master": (_i, [_tp, _i, _i, _d, _i, _vp, _vp, _d, _vp]),
     "apex_b200_mt_master_to_model": (_i, [_tp, _i, _i, _vp, _vp]),
     "apex_b200_mt_copy": (_i, [_tp, _i, _i, _i, _vp, _vp]),
     "apex_b200_mt_zero": (_i, [_tp, _i, _i, _vp]),
@@ -171,10 +171,13 @@ def mt_unscale(table, grad_list, inv_scale, flag, mode, stream=None):
                                     current_stream() if stream is None else stream), "mt_unscale")
 
 
-def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, stream=None):
+def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, clip=None, stream=None):
+    """clip: None or (device norm tensor, max_norm)."""
     _count(table)
     _check(lib.apex_b200_mt_grads_to_master(table.ref, src_list, dst_list, float(inv_scale), int(apply_scale),
-                                            _ptr(flag), current_stream() if stream is None else stream),
+                                            _ptr(flag), None if clip is None else _ptr(clip[0]),
+                                            0.0 if clip is None else float(clip[1]),
+                                            current_stream() if stream is None else stream),
            "mt_grads_to_master")
 
 
@@ -197,20 +200,21 @@ def mt_zero(table, lst, elem_size, stream=None):
 
 
 def mt_fused_sgd(table, lr, momentum, dampening, weight_decay, nesterov, inv_scale, apply_scale, flag,
-                 stream=None):
+                 clip=None, stream=None):
     _count(table)
     a = SgdArgs(float(lr), float(momentum), float(dampening), float(weight_decay), int(bool(nesterov)),
-                int(bool(apply_scale)), float(inv_scale))
+                int(bool(apply_scale)), float(inv_scale), None if clip is None else _ptr(clip[0]),
+                0.0 if clip is None else float(clip[1]))
     _check(lib.apex_b200_mt_fused_sgd(table.ref, ctypes.byref(a), _ptr(flag),
                                       current_stream() if stream is None else stream), "mt_fused_sgd")
 
 
 def mt_fused_adam(table, lr, beta1, beta2, eps, weight_decay, step_size, bias_correction2_sqrt,
-                  decoupled_weight_decay, inv_scale, apply_scale, flag, stream=None):
+                  decoupled_weight_decay, inv_scale, apply_scale, flag, clip=None, stream=None):
     _count(table)
     a = AdamArgs(float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(step_size),
                  float(bias_correction2_sqrt), int(bool(decoupled_weight_decay)), int(bool(apply_scale)),
-                 float(inv_scale))
+                 float(inv_scale), None if clip is None else _ptr(clip[0]), 0.0 if clip is None else float(clip[1]))
     _check(lib.apex_b200_mt_fused_adam(table.ref, ctypes.byref(a), _ptr(flag),
                                        current_stream() if stream is None else stream), "mt_fused_adam")
 

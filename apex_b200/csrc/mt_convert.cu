@@ -13,8 +13,17 @@ namespace apex_b200 {
 
 __global__ void __launch_bounds__(kThreads)
 mt_grads_to_master_kernel(MtView v, int src_list, int dst_list, float inv_scale,
-                          int apply_scale, const int32_t* __restrict__ flag) {
+                          int apply_scale, const int32_t* __restrict__ flag,
+                          const float* __restrict__ clip_norm, float clip_max_norm) {
     if (flag != nullptr && *flag != 0) return;
+    // optional second factor: clip_grad_norm_'s clamp(max_norm / (norm + 1e-6), max=1)
+    float coef = 1.0f;
+    if (clip_norm != nullptr) {
+        coef = __fdiv_rn(clip_max_norm, __fadd_rn(__ldg(clip_norm), 1e-6f));
+        coef = coef > 1.0f ? 1.0f : coef;
+        apply_scale = 1;
+    }
+    if (clip_norm == nullptr && !apply_scale) inv_scale = 1.0f;
     for (int chunk = blockIdx.x; chunk < v.total_chunks; chunk += gridDim.x) {
         const MtChunk c = mt_locate(v, chunk);
         const __half* s = mt_ptr<const __half>(v, src_list, c.tensor) + c.offset;
@@ -31,7 +40,7 @@ mt_grads_to_master_kernel(MtView v, int src_list, int dst_list, float inv_scale,
                     F8 f = h8_to_f8(h[u]);
                     if (apply_scale) {
 #pragma unroll
-                        for (int k = 0; k < 8; ++k) f.v[k] = __fmul_rn(f.v[k], inv_scale);
+                        for (int k = 0; k < 8; ++k) f.v[k] = __fmul_rn(__fmul_rn(f.v[k], inv_scale), coef);
                     }
                     st_f8(d + size_t(i + u * kThreads) * kVec, f);
                 }
@@ -40,19 +49,19 @@ mt_grads_to_master_kernel(MtView v, int src_list, int dst_list, float inv_scale,
                 F8 f = h8_to_f8(ld_h8(s + size_t(i) * kVec));
                 if (apply_scale) {
 #pragma unroll
-                    for (int k = 0; k < 8; ++k) f.v[k] = __fmul_rn(f.v[k], inv_scale);
+                    for (int k = 0; k < 8; ++k) f.v[k] = __fmul_rn(__fmul_rn(f.v[k], inv_scale), coef);
                 }
                 st_f8(d + size_t(i) * kVec, f);
             }
             const int t = (nvec << 3) + threadIdx.x;
             if (t < c.len) {
                 float x = __half2float(s[t]);
-                d[t] = apply_scale ? __fmul_rn(x, inv_scale) : x;
+                d[t] = apply_scale ? __fmul_rn(__fmul_rn(x, inv_scale), coef) : x;
             }
         } else {
             for (int i = threadIdx.x; i < c.len; i += kThreads) {
                 float x = __half2float(s[i]);
-                d[i] = apply_scale ? __fmul_rn(x, inv_scale) : x;
+                d[i] = apply_scale ? __fmul_rn(__fmul_rn(x, inv_scale), coef) : x;
             }
         }
     }
@@ -291,13 +300,15 @@ using namespace apex_b200;
 
 extern "C" int apex_b200_mt_grads_to_master(const apex_b200_mt_table* t, int src_list, int dst_list,
                                             double inv_scale, int apply_scale,
-                                            const int32_t* d_flag, void* stream) {
+                                            const int32_t* d_flag, const float* d_clip_norm,
+                                            double clip_max_norm, void* stream) {
     if (t == nullptr) return APEX_B200_EINVAL;
     APEX_CHECK_LIST(t, src_list);
     APEX_CHECK_LIST(t, dst_list);
     APEX_CHECK_TABLE(t);
     mt_grads_to_master_kernel<<<mt_grid(t->total_chunks, 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        mt_view(t), src_list, dst_list, static_cast<float>(inv_scale), apply_scale, d_flag);
+        mt_view(t), src_list, dst_list, static_cast<float>(inv_scale), apply_scale, d_flag, d_clip_norm,
+        static_cast<float>(clip_max_norm));
     return mt_cuda_status();
 }
 

@@ -29,18 +29,32 @@ namespace apex_b200 {
 struct SgdHp {
     float neg_lr, momentum, one_minus_dampening, weight_decay, inv_scale;
     int use_wd, use_momentum, nesterov, apply_scale;
+    const float* clip_norm;     // device: total gradient norm, or nullptr (no clipping)
+    float clip_max_norm;
 };
 
 struct AdamHp {
     float beta2, one_minus_beta2, lerp_w, one_minus_lerp_w, eps, weight_decay, decay_mul;
     float step_size, bc2_sqrt, inv_scale;
     int use_wd, decoupled, lerp_small, apply_scale;
+    const float* clip_norm;
+    float clip_max_norm;
 };
+
+// torch.nn.utils.clip_grad_norm_: every gradient is multiplied by
+// clamp(max_norm / (total_norm + 1e-6), max=1.0) -- always, also when it is 1 (a NaN norm
+// poisons the gradients there, and here).  1.0f when no clipping was asked for.
+__device__ __forceinline__ float clip_coef(const float* norm, float max_norm) {
+    if (norm == nullptr) return 1.0f;
+    const float c = __fdiv_rn(max_norm, __fadd_rn(__ldg(norm), 1e-6f));
+    return c > 1.0f ? 1.0f : c;      // NaN stays NaN
+}
 
 // torch/optim/sgd.py:425-468 (foreach) == :333-380 (single tensor)
 template <bool kMom>
-__device__ __forceinline__ void sgd_elem(float g, float& p, float& buf, const SgdHp& h, bool first, float inv) {
+__device__ __forceinline__ void sgd_elem(float g, float& p, float& buf, const SgdHp& h, bool first, float inv, float coef) {
     g = __fmul_rn(g, inv);                                          // grad.mul_(1./loss_scale); inv == 1 is exact
+    g = __fmul_rn(g, coef);                                         // clip_grad_norm_'s mul_; coef == 1 is exact
     if (h.use_wd) g = __fmaf_rn(h.weight_decay, p, g);              // _foreach_add(grads, params, alpha=wd)
     if (kMom) {
         if (first) {
@@ -55,8 +69,9 @@ __device__ __forceinline__ void sgd_elem(float g, float& p, float& buf, const Sg
 }
 
 // torch/optim/adam.py:686-800 (foreach, capturable=False, amsgrad=False)
-__device__ __forceinline__ void adam_elem(float g, float& p, float& m, float& v, const AdamHp& h, float inv) {
+__device__ __forceinline__ void adam_elem(float g, float& p, float& m, float& v, const AdamHp& h, float inv, float coef) {
     g = __fmul_rn(g, inv);
+    g = __fmul_rn(g, coef);
     if (h.use_wd) {
         if (h.decoupled) p = __fmul_rn(p, h.decay_mul);             // _foreach_mul_(params, 1 - lr*wd)
         else g = __fmaf_rn(h.weight_decay, p, g);                   // _foreach_add(grads, params, alpha=wd)
@@ -81,6 +96,7 @@ template <typename G, bool kModel, bool kMom>
 __device__ __forceinline__ void sgd_chunk(const MtView& v, const MtChunk& c, const SgdHp& h) {
     const bool first = c.flags & APEX_B200_TF_FIRST_STEP;
     const float inv = (h.apply_scale && !(c.flags & APEX_B200_TF_NO_SCALE)) ? h.inv_scale : 1.0f;
+    const float coef = (c.flags & APEX_B200_TF_NO_SCALE) ? 1.0f : clip_coef(h.clip_norm, h.clip_max_norm);
     const G* g = mt_ptr<const G>(v, 0, c.tensor) + c.offset;
     float* p = mt_ptr<float>(v, 1, c.tensor) + c.offset;
     float* b = kMom ? mt_ptr<float>(v, 2, c.tensor) + c.offset : nullptr;
@@ -104,7 +120,7 @@ __device__ __forceinline__ void sgd_chunk(const MtView& v, const MtChunk& c, con
             for (int u = 0; u < kStepUnroll; ++u) {
                 const size_t e = size_t(i + u * kThreads) * kVec;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) sgd_elem<kMom>(gv[u].v[k], pv[u].v[k], bv[u].v[k], h, first, inv);
+                for (int k = 0; k < 8; ++k) sgd_elem<kMom>(gv[u].v[k], pv[u].v[k], bv[u].v[k], h, first, inv, coef);
                 st_f8(p + e, pv[u]);
                 if (kMom) st_f8(b + e, bv[u]);
                 if (kModel) st_h8(q + e, f8_to_h8(pv[u]));
@@ -117,7 +133,7 @@ __device__ __forceinline__ void sgd_chunk(const MtView& v, const MtChunk& c, con
                 F8 gv = GradIo<G>::ld8(g + e), pv = ld_f8(p + e), bv = F8{};
                 if (read_buf) bv = ld_f8(b + e);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) sgd_elem<kMom>(gv.v[k], pv.v[k], bv.v[k], h, first, inv);
+                for (int k = 0; k < 8; ++k) sgd_elem<kMom>(gv.v[k], pv.v[k], bv.v[k], h, first, inv, coef);
                 st_f8(p + e, pv);
                 if (kMom) st_f8(b + e, bv);
                 if (kModel) st_h8(q + e, f8_to_h8(pv));
@@ -126,7 +142,7 @@ __device__ __forceinline__ void sgd_chunk(const MtView& v, const MtChunk& c, con
         const int t = (nvec << 3) + threadIdx.x;
         if (t < c.len) {
             float pe = p[t], be = read_buf ? b[t] : 0.f;
-            sgd_elem<kMom>(GradIo<G>::ld1(g + t), pe, be, h, first, inv);
+            sgd_elem<kMom>(GradIo<G>::ld1(g + t), pe, be, h, first, inv, coef);
             p[t] = pe;
             if (kMom) b[t] = be;
             if (kModel) q[t] = __float2half_rn(pe);
@@ -135,7 +151,7 @@ __device__ __forceinline__ void sgd_chunk(const MtView& v, const MtChunk& c, con
 #pragma unroll 1
         for (int i = threadIdx.x; i < c.len; i += kThreads) {
             float pe = p[i], be = read_buf ? b[i] : 0.f;
-            sgd_elem<kMom>(GradIo<G>::ld1(g + i), pe, be, h, first, inv);
+            sgd_elem<kMom>(GradIo<G>::ld1(g + i), pe, be, h, first, inv, coef);
             p[i] = pe;
             if (kMom) b[i] = be;
             if (kModel) q[i] = __float2half_rn(pe);
@@ -163,6 +179,7 @@ mt_fused_sgd_kernel(MtView v, SgdHp h, const int32_t* __restrict__ flag) {
 template <typename G, bool kModel>
 __device__ __forceinline__ void adam_chunk(const MtView& v, const MtChunk& c, const AdamHp& h) {
     const float inv = (h.apply_scale && !(c.flags & APEX_B200_TF_NO_SCALE)) ? h.inv_scale : 1.0f;
+    const float coef = (c.flags & APEX_B200_TF_NO_SCALE) ? 1.0f : clip_coef(h.clip_norm, h.clip_max_norm);
     const G* g = mt_ptr<const G>(v, 0, c.tensor) + c.offset;
     float* p = mt_ptr<float>(v, 1, c.tensor) + c.offset;
     float* m = mt_ptr<float>(v, 2, c.tensor) + c.offset;
@@ -187,7 +204,7 @@ __device__ __forceinline__ void adam_chunk(const MtView& v, const MtChunk& c, co
             for (int u = 0; u < kStepUnroll; ++u) {
                 const size_t e = size_t(i + u * kThreads) * kVec;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) adam_elem(gv[u].v[k], pv[u].v[k], mv[u].v[k], sv[u].v[k], h, inv);
+                for (int k = 0; k < 8; ++k) adam_elem(gv[u].v[k], pv[u].v[k], mv[u].v[k], sv[u].v[k], h, inv, coef);
                 st_f8(p + e, pv[u]);
                 st_f8(m + e, mv[u]);
                 st_f8(s + e, sv[u]);
@@ -199,7 +216,7 @@ __device__ __forceinline__ void adam_chunk(const MtView& v, const MtChunk& c, co
             const size_t e = size_t(i) * kVec;
             F8 gv = GradIo<G>::ld8(g + e), pv = ld_f8(p + e), mv = ld_f8(m + e), sv = ld_f8(s + e);
 #pragma unroll
-            for (int k = 0; k < 8; ++k) adam_elem(gv.v[k], pv.v[k], mv.v[k], sv.v[k], h, inv);
+            for (int k = 0; k < 8; ++k) adam_elem(gv.v[k], pv.v[k], mv.v[k], sv.v[k], h, inv, coef);
             st_f8(p + e, pv);
             st_f8(m + e, mv);
             st_f8(s + e, sv);
@@ -208,7 +225,7 @@ __device__ __forceinline__ void adam_chunk(const MtView& v, const MtChunk& c, co
         const int t = (nvec << 3) + threadIdx.x;
         if (t < c.len) {
             float pe = p[t], me = m[t], se = s[t];
-            adam_elem(GradIo<G>::ld1(g + t), pe, me, se, h, inv);
+            adam_elem(GradIo<G>::ld1(g + t), pe, me, se, h, inv, coef);
             p[t] = pe; m[t] = me; s[t] = se;
             if (kModel) q[t] = __float2half_rn(pe);
         }
@@ -216,7 +233,7 @@ __device__ __forceinline__ void adam_chunk(const MtView& v, const MtChunk& c, co
 #pragma unroll 1
         for (int i = threadIdx.x; i < c.len; i += kThreads) {
             float pe = p[i], me = m[i], se = s[i];
-            adam_elem(GradIo<G>::ld1(g + i), pe, me, se, h, inv);
+            adam_elem(GradIo<G>::ld1(g + i), pe, me, se, h, inv, coef);
             p[i] = pe; m[i] = me; s[i] = se;
             if (kModel) q[i] = __float2half_rn(pe);
         }
@@ -259,6 +276,8 @@ extern "C" int apex_b200_mt_fused_sgd(const apex_b200_mt_table* t, const apex_b2
     h.inv_scale = static_cast<float>(a->inv_scale);
     h.nesterov = a->nesterov != 0;
     h.apply_scale = a->apply_scale != 0;
+    h.clip_norm = a->clip_norm;
+    h.clip_max_norm = static_cast<float>(a->clip_max_norm);
     const int grid = mt_grid(t->total_chunks, 4);
     cudaStream_t s = static_cast<cudaStream_t>(stream);
     if (h.use_momentum) mt_fused_sgd_kernel<true><<<grid, kThreads, 0, s>>>(mt_view(t), h, d_flag);
@@ -287,6 +306,8 @@ extern "C" int apex_b200_mt_fused_adam(const apex_b200_mt_table* t, const apex_b
     h.use_wd = a->weight_decay != 0.0;
     h.decoupled = a->decoupled_weight_decay != 0;
     h.apply_scale = a->apply_scale != 0;
+    h.clip_norm = a->clip_norm;
+    h.clip_max_norm = static_cast<float>(a->clip_max_norm);
     mt_fused_adam_kernel<<<mt_grid(t->total_chunks, 4), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
         mt_view(t), h, d_flag);
     return mt_cuda_status();

@@ -34,8 +34,8 @@ import weakref
 import torch
 
 from .. import _C
-from ..multi_tensor import (TensorTable, CHUNK_STEP, CHUNK_STREAM, CHUNK_CHECK, CHUNK_ZERO, new_flag,
-                            same_objects)
+from ..multi_tensor import (TensorTable, CHUNK_STEP, CHUNK_STREAM, CHUNK_CHECK, CHUNK_ZERO, CHUNK_NORM,
+                            new_flag, same_objects)
 from .loss_scaler import DynamicLossScaler, LossScaler
 from .fp16util import master_params_to_model_params, clip_grad_norm
 
@@ -286,6 +286,7 @@ class FP16_Optimizer(object):
         self.fp32_from_fp32_groups = []
         self._pending = None          # (inv_scale, apply_scale): master grads are float(g16)*inv_scale, not stored
         self._grads_ready = False     # master grads are materialised and current
+        self._clip = None             # (device norm, max_norm): clipping still to be applied to virtual grads
         self_ref = weakref.ref(self)
         for gi, param_group in enumerate(self.optimizer.param_groups):
             self.maybe_print("FP16_Optimizer processing param group {}:".format(gi))
@@ -347,7 +348,9 @@ class FP16_Optimizer(object):
         self._step_tables = {}           # group index -> table for the fused step
         self._plans = {}                 # group index -> cached _StepPlan
         self._zero_table = None
-        self._norm_buf = None
+        self._norm_buf = None            # [norm, per-chunk partial sums...] scratch of the gradient norm
+        self._norm_table = None
+        self._clip_table = None
 
     # ---- small helpers -------------------------------------------------------
 
@@ -394,6 +397,7 @@ class FP16_Optimizer(object):
         """Zero (or drop) fp32 and fp16 gradients (reference: :187-211), in one launch."""
         self._pending = None
         self._grads_ready = False
+        self._clip = None
         if set_grads_to_None:
             for group in self.optimizer.param_groups:
                 for p in group['params']:
@@ -493,6 +497,7 @@ class FP16_Optimizer(object):
         ``_model_grads_to_master_grads`` + ``_downscale_master`` for the masters
         (:232-241), including its early return on overflow (:493-495)."""
         pending, self._pending = self._pending, None
+        clip, self._clip = self._clip, None
         if pending is None:
             return
         inv_scale, apply_scale = pending
@@ -518,7 +523,7 @@ class FP16_Optimizer(object):
             if table is None:
                 table = self._grad_tables[gi] = TensorTable(self._device, 2, CHUNK_STREAM)
             table.update([srcs, dsts])
-            _C.mt_grads_to_master(table, 0, 1, inv_scale, apply_scale, None)
+            _C.mt_grads_to_master(table, 0, 1, inv_scale, apply_scale, None, clip)
 
     def _model_grads_to_master_grads(self):
         # kept for API parity with the reference (:232-234); scale 1 = plain copy
@@ -555,16 +560,63 @@ class FP16_Optimizer(object):
     def clip_master_grads(self, max_norm, norm_type=2):
         """Clip the fp32 master gradients (reference: :243-265).
 
-        Returns the total norm, or -1 if the last gradients overflowed.
+        Returns the total norm, or -1 if the last gradients overflowed.  For the 2-norm the
+        norm is computed straight from the fp16 gradients (one read of 2 B/param) and the
+        clipping factor is applied inside the fused update: the master gradients are still
+        not written unless somebody looks at them.
         """
-        if not self.overflow:
-            fp32_params = []
-            for param_group in self.optimizer.param_groups:
-                for param in param_group['params']:
-                    fp32_params.append(param)
-            return self.clip_grad_norm(fp32_params, max_norm, norm_type)
-        else:
+        if self.overflow:
             return -1
+        if self._pending is not None and self._clip is None and norm_type in (2, 2.0) \
+                and self.clip_grad_norm is clip_grad_norm:
+            return self._clip_virtual(max_norm)
+        fp32_params = []
+        for param_group in self.optimizer.param_groups:
+            for param in param_group['params']:
+                fp32_params.append(param)
+        return self.clip_grad_norm(fp32_params, max_norm, norm_type)
+
+    def _clip_virtual(self, max_norm):
+        inv_scale, apply_scale = self._pending
+        grads, flags, floats = [], [], []
+        for group in self.fp16_groups:
+            for param in group:
+                g = param.grad
+                if g is not None:
+                    grads.append(g)
+                    flags.append(0)
+        for group in self.fp32_from_fp32_groups:
+            for param in group:
+                g = param.grad
+                if g is not None:
+                    grads.append(g)
+                    floats.append(g)
+                    flags.append(_C.TF_GRAD_F32 | _C.TF_NO_SCALE)     # unscaled in place already
+        if not grads:
+            return torch.zeros(())
+        self._ensure_device(grads[0])
+        table = self._norm_table
+        if table is None:
+            table = self._norm_table = TensorTable(self._device, 1, CHUNK_NORM)
+        if not table.built_from(grads):
+            table.update([grads], flags)
+            table.remember(grads)
+        chunks = table.struct.total_chunks
+        if self._norm_buf is None or self._norm_buf.numel() < chunks + 1:
+            self._norm_buf = torch.empty(chunks + 1, dtype=torch.float32, device=self._device)
+        norm, partials = self._norm_buf[:1], self._norm_buf[1:]
+        _C.mt_l2norm(table, 0, inv_scale, apply_scale, partials, norm)
+        if floats:
+            # the user's own fp32 gradients are clipped where they are, as torch does
+            ftable = self._clip_table
+            if ftable is None:
+                ftable = self._clip_table = TensorTable(self._device, 1, CHUNK_STREAM)
+            if not ftable.built_from(floats):
+                ftable.update([floats], [_C.TF_GRAD_F32] * len(floats))
+                ftable.remember(floats)
+            _C.mt_clip_by_norm(ftable, 0, norm, max_norm, None)
+        self._clip = (norm, max_norm)
+        return norm[0].clone()
 
     # ---- checkpointing --------------------------------------------------------------------
 
@@ -583,6 +635,7 @@ class FP16_Optimizer(object):
         """Restore scaler, flags, inner optimizer and the saved fp32 masters (reference: :288-328)."""
         self._pending = None
         self._grads_ready = False
+        self._clip = None
         self.loss_scaler = state_dict['loss_scaler']
         self.dynamic_loss_scale = state_dict['dynamic_loss_scale']
         self.overflow = state_dict['overflow']
@@ -677,6 +730,7 @@ class FP16_Optimizer(object):
             return None           # overflow already known on the host: step() skips
         from_masters = pending is None     # gradients were materialised (e.g. for clipping)
         inv_scale, apply_scale = (1.0, False) if from_masters else pending
+        clip = None if from_masters else self._clip
         plans = []
         for gi, group in enumerate(self.optimizer.param_groups):
             plan = self._plan_for(kind, gi, group, from_masters)
@@ -688,7 +742,7 @@ class FP16_Optimizer(object):
         for group, plan in plans:
             if kind == "sgd":
                 _C.mt_fused_sgd(plan.table, group['lr'], group['momentum'], group['dampening'],
-                                group['weight_decay'], group['nesterov'], inv_scale, apply_scale, flag)
+                                group['weight_decay'], group['nesterov'], inv_scale, apply_scale, flag, clip)
             else:
                 beta1, beta2 = group['betas']
                 step = plan.step_count() + 1
@@ -698,7 +752,8 @@ class FP16_Optimizer(object):
                 step_size = (group['lr'] / bias_correction1) * -1
                 _C.mt_fused_adam(plan.table, group['lr'], beta1, beta2, group['eps'], group['weight_decay'],
                                  step_size, bias_correction2 ** 0.5,
-                                 bool(group.get('decoupled_weight_decay', False)), inv_scale, apply_scale, flag)
+                                 bool(group.get('decoupled_weight_decay', False)), inv_scale, apply_scale, flag,
+                                 clip)
 
         def commit():
             for _, plan in plans:
@@ -751,6 +806,7 @@ class FP16_Optimizer(object):
         masters (reference: :486-497)."""
         self._pending = None
         self._grads_ready = False
+        self._clip = None
         if self.dynamic_loss_scale:
             self._check_overflow()
             # reference: `if self.overflow: return`.  The decision is still on the

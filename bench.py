@@ -351,6 +351,7 @@ def main():
 
     t_check = Timed(_C, "mt_check_overflow")
     t_fused = Timed(_C, FUSED_WRAPPER[kind])
+    t_ar = Timed(_C, "symm_allreduce")
 
     for _ in range(args.warmup):
         step()
@@ -361,7 +362,7 @@ def main():
     if rank == 0:
         sampler.start()
         time.sleep(0.3)
-    t_check.on = t_fused.on = True
+    t_check.on = t_fused.on = t_ar.on = True
     del comm_events[:]
     host_s[0] = 0.0
     launches0 = _C.launches
@@ -378,7 +379,7 @@ def main():
     elapsed_ms = start.elapsed_time(stop)
     host_ms_per_step = host_s[0] / args.steps * 1e3      # python time inside step(), timed region only
     launches = _C.launches - launches0
-    t_check.on = t_fused.on = False
+    t_check.on = t_fused.on = t_ar.on = False
     clocks = sampler.stop() if rank == 0 else None
     if world > 1:
         t = torch.tensor([elapsed_ms], device=dev, dtype=torch.float64)
@@ -462,11 +463,24 @@ def main():
         if comm_ms:
             s_bytes = 2 * n_params
             algbw = s_bytes / (comm_ms * 1e-3) / 1e9
+            from apex_b200.parallel import symm as _symm
+            kernel = None
+            if t_ar.count():
+                k_ms = t_ar.total_ms() / args.steps          # our allreduce kernels of one step, summed
+                k_alg = s_bytes / (k_ms * 1e-3) / 1e9
+                kernel = {"ms_per_step": k_ms, "launches_per_step": t_ar.count() / args.steps, "algbw_gbs": k_alg,
+                          "busbw_gbs": k_alg * 2 * (world - 1) / world,
+                          "frac_of_900": k_alg * 2 * (world - 1) / world / 900.0,
+                          "what": "apex_b200_symm_allreduce launches only (CUDA events on their stream); they "
+                                  "overlap the gather/scatter kernels of neighbouring buckets"}
             line["allreduce"] = {"bytes": s_bytes, "ms": comm_ms, "algbw_gbs": algbw,
+                                 "transport": "apex_b200 symmetric-memory two-shot (NVSwitch multimem beyond 2 "
+                                              "ranks, peer-to-peer at 2)" if _symm.enabled() else "NCCL",
+                                 "kernel": kernel,
                                  "busbw_gbs": algbw * 2 * (world - 1) / world, "nvlink_peak_gbs_per_dir": 900.0,
                                  "frac_of_900": algbw * 2 * (world - 1) / world / 900.0,
-                                 "includes": "gather + NCCL all_reduce + x(1/N) scatter per bucket, the three stages "
-                                             "of consecutive buckets overlapped on side streams"}
+                                 "includes": "whole bucket path: gather + allreduce + x(1/N) scatter per bucket, the "
+                                             "three stages of consecutive buckets overlapped on side streams"}
         print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()

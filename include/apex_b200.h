@@ -130,10 +130,14 @@ int apex_b200_mt_unscale(const apex_b200_mt_table* t, int grad_list,
 /* Replaces model_grads_to_master_grads (apex/fp16_utils/fp16util.py:93-112)
  * fused with _downscale_master (fp16_optimizer.py:236-241):
  * dst32[i] = float(src16[i]) * inv_scale (exact widening when apply_scale == 0).
+ * With d_clip_norm != NULL the result is further multiplied by
+ * clamp(clip_max_norm / (*d_clip_norm + 1e-6), max=1), the factor of
+ * clip_master_grads (fp16_optimizer.py:243-265 -> torch clip_grad_norm_).
  * Skipped entirely when d_flag != NULL and *d_flag != 0. */
 int apex_b200_mt_grads_to_master(const apex_b200_mt_table* t, int src_list,
                                  int dst_list, double inv_scale, int apply_scale,
-                                 const int32_t* d_flag, void* stream);
+                                 const int32_t* d_flag, const float* d_clip_norm,
+                                 double clip_max_norm, void* stream);
 
 /* Replaces master_params_to_model_params (apex/fp16_utils/fp16util.py:115-129):
  * dst16[i] = half_rn(src32[i]).  Skipped when d_flag != NULL and *d_flag != 0. */
@@ -172,6 +176,10 @@ typedef struct apex_b200_sgd_args {
     int32_t nesterov;
     int32_t apply_scale;      /* 0: gradient is used as is */
     double inv_scale;         /* 1./loss_scale as a python double */
+    const float* clip_norm;   /* device: total norm from apex_b200_mt_l2norm, or NULL.  The unscaled
+                                 gradient is multiplied by clamp(clip_max_norm/(norm+1e-6), max=1):
+                                 clip_master_grads (fp16_optimizer.py:243-265) folded into the step */
+    double clip_max_norm;
 } apex_b200_sgd_args;
 
 int apex_b200_mt_fused_sgd(const apex_b200_mt_table* t,
@@ -190,6 +198,8 @@ typedef struct apex_b200_adam_args {
     int32_t decoupled_weight_decay;
     int32_t apply_scale;
     double inv_scale;
+    const float* clip_norm;   /* as in apex_b200_sgd_args */
+    double clip_max_norm;
 } apex_b200_adam_args;
 
 int apex_b200_mt_fused_adam(const apex_b200_mt_table* t,

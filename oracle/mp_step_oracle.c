@@ -43,6 +43,15 @@ void ora_f16_to_f32_scaled(const uint16_t* g, float* out, long long n, double in
     const float inv = (float)inv_scale;
     for (long long i = 0; i < n; ++i) { float x = h2f(g[i]); out[i] = apply ? x * inv : x; }
 }
+/* the factor torch.nn.utils.clip_grad_norm_ multiplies every gradient by (fp32 arithmetic) */
+float ora_clip_coef(float total_norm, double max_norm) {
+    const float c = (float)max_norm / (total_norm + 1e-6f);
+    return c > 1.0f ? 1.0f : c;
+}
+void ora_f16_to_f32_scaled_clipped(const uint16_t* g, float* out, long long n, double inv_scale, float coef) {
+    const float inv = (float)inv_scale;
+    for (long long i = 0; i < n; ++i) { float x = h2f(g[i]) * inv; out[i] = x * coef; }
+}
 void ora_scale_f32(float* g, long long n, double inv_scale) {
     const float inv = (float)inv_scale;
     for (long long i = 0; i < n; ++i) g[i] = g[i] * inv;
@@ -55,12 +64,13 @@ void ora_f32_to_f16(const float* p, uint16_t* out, long long n) {
  * p16 may be NULL.  first != 0: momentum buffer is initialised from the gradient. */
 void ora_sgd(const uint16_t* g16, const float* g32, float* p, float* buf, uint16_t* p16, long long n,
              double lr, double momentum, double dampening, double weight_decay, int nesterov,
-             int first, double inv_scale, int apply_scale) {
+             int first, double inv_scale, int apply_scale, float clip_coef, int apply_clip) {
     const float neg_lr = (float)(-lr), mom = (float)momentum, omd = (float)(1.0 - dampening);
     const float wd = (float)weight_decay, inv = (float)inv_scale;
     for (long long i = 0; i < n; ++i) {
         float g = g16 ? h2f(g16[i]) : g32[i];
         if (apply_scale) g = g * inv;
+        if (apply_clip) g = g * clip_coef;
         if (weight_decay != 0.0) g = fmaf(wd, p[i], g);
         if (momentum != 0.0) {
             float b;
@@ -84,7 +94,7 @@ void ora_sgd(const uint16_t* g16, const float* g32, float* p, float* buf, uint16
 void ora_adam_flavour(const uint16_t* g16, const float* g32, float* p, float* m, float* v, uint16_t* p16, long long n,
               double lr, double beta1, double beta2, double eps, double weight_decay,
               double step_size, double bc2_sqrt, int decoupled, double inv_scale, int apply_scale,
-              int flavour, int cpu_fma) {
+              int flavour, int cpu_fma, float clip_coef, int apply_clip) {
     const float w = (float)(1.0 - beta1), b2 = (float)beta2, omb2 = (float)(1.0 - beta2);
     const float one_minus_w = 1.0f - w;
     const float e = (float)eps, wd = (float)weight_decay, decay = (float)(1.0 - lr * weight_decay);
@@ -93,6 +103,7 @@ void ora_adam_flavour(const uint16_t* g16, const float* g32, float* p, float* m,
     for (long long i = 0; i < n; ++i) {
         float g = g16 ? h2f(g16[i]) : g32[i];
         if (apply_scale) g = g * inv;
+        if (apply_clip) g = g * clip_coef;
         if (weight_decay != 0.0) {
             if (decoupled) p[i] = p[i] * decay;
             else g = fmaf(wd, p[i], g);
@@ -116,7 +127,7 @@ void ora_adam(const uint16_t* g16, const float* g32, float* p, float* m, float* 
               double lr, double beta1, double beta2, double eps, double weight_decay,
               double step_size, double bc2_sqrt, int decoupled, double inv_scale, int apply_scale) {
     ora_adam_flavour(g16, g32, p, m, v, p16, n, lr, beta1, beta2, eps, weight_decay, step_size, bc2_sqrt,
-                     decoupled, inv_scale, apply_scale, 0, 0);
+                     decoupled, inv_scale, apply_scale, 0, 0, 1.0f, 0);
 }
 
 /* x *= float(1/divisor) in the bucket dtype */

@@ -63,12 +63,16 @@ def mt_unscale(table, grad_list, inv_scale, flag, mode, stream=None):
             _flat(g)[:] = c_oracle.f32_to_f16(f)
 
 
-def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, stream=None):
+def _coef(clip):
+    return None if clip is None else c_oracle.clip_coef(float(clip[0][0]), clip[1])
+
+
+def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, clip=None, stream=None):
     calls.append("grads_to_master")
     if _flag_set(flag):
         return
     for s, d in zip(table.lists[src_list], table.lists[dst_list]):
-        _flat(d)[:] = c_oracle.f16_to_f32_scaled(_flat(s), inv_scale, bool(apply_scale))
+        _flat(d)[:] = c_oracle.f16_to_f32_scaled(_flat(s), inv_scale, bool(apply_scale), _coef(clip))
 
 
 def mt_master_to_model(table, src_list, dst_list, flag, stream=None):
@@ -94,7 +98,7 @@ def mt_zero(table, lst, elem_size, stream=None):
 
 
 def mt_fused_sgd(table, lr, momentum, dampening, weight_decay, nesterov, inv_scale, apply_scale, flag,
-                 stream=None):
+                 clip=None, stream=None):
     calls.append("fused_sgd")
     if _flag_set(flag):
         return
@@ -104,13 +108,14 @@ def mt_fused_sgd(table, lr, momentum, dampening, weight_decay, nesterov, inv_sca
         apply = bool(apply_scale) and not (fl & _C.TF_NO_SCALE)
         buf = None if bufs[i] is None else _flat(bufs[i])
         p16 = c_oracle.sgd(_flat(grads[i]), _flat(params[i]), buf, lr, momentum, dampening, weight_decay,
-                           nesterov, first=bool(fl & _C.TF_FIRST_STEP), inv_scale=inv_scale, apply_scale=apply)
+                           nesterov, first=bool(fl & _C.TF_FIRST_STEP), inv_scale=inv_scale, apply_scale=apply,
+                           clip_coef=None if (fl & _C.TF_NO_SCALE) else _coef(clip))
         if not (fl & _C.TF_NO_MODEL):
             _flat(models[i])[:] = p16
 
 
 def mt_fused_adam(table, lr, beta1, beta2, eps, weight_decay, step_size, bias_correction2_sqrt,
-                  decoupled_weight_decay, inv_scale, apply_scale, flag, stream=None):
+                  decoupled_weight_decay, inv_scale, apply_scale, flag, clip=None, stream=None):
     calls.append("fused_adam")
     if _flag_set(flag):
         return
@@ -122,11 +127,13 @@ def mt_fused_adam(table, lr, beta1, beta2, eps, weight_decay, step_size, bias_co
         g = _flat(grads[i])
         p = _flat(params[i])
         p16 = np.empty(p.shape, np.uint16)
-        lib.ora_adam(g.ctypes.data if g.dtype == np.uint16 else None,
-                     g.ctypes.data if g.dtype == np.float32 else None,
-                     p.ctypes.data, _flat(ms[i]).ctypes.data, _flat(vs[i]).ctypes.data, p16.ctypes.data, p.size,
-                     float(lr), float(beta1), float(beta2), float(eps), float(weight_decay), float(step_size),
-                     float(bias_correction2_sqrt), int(bool(decoupled_weight_decay)), float(inv_scale), int(apply))
+        coef = None if (fl & _C.TF_NO_SCALE) else _coef(clip)
+        lib.ora_adam_flavour(g.ctypes.data if g.dtype == np.uint16 else None,
+                             g.ctypes.data if g.dtype == np.float32 else None,
+                             p.ctypes.data, _flat(ms[i]).ctypes.data, _flat(vs[i]).ctypes.data, p16.ctypes.data,
+                             p.size, float(lr), float(beta1), float(beta2), float(eps), float(weight_decay),
+                             float(step_size), float(bias_correction2_sqrt), int(bool(decoupled_weight_decay)),
+                             float(inv_scale), int(apply), 0, 0, 1.0 if coef is None else coef, int(coef is not None))
         if not (fl & _C.TF_NO_MODEL):
             _flat(models[i])[:] = p16
 
@@ -192,11 +199,11 @@ def mt_clip_by_norm(table, grad_list, norm, max_norm, flag, stream=None):
     calls.append("clip")
     if _flag_set(flag):
         return
-    coef = np.float32(max_norm) / (np.float32(norm[0]) + np.float32(1e-6))
+    coef = np.float32(c_oracle.clip_coef(float(norm[0]), max_norm))
     if coef >= 1.0:
         return
     for g in table.lists[grad_list]:
-        _flat(g)[:] = _flat(g) * np.float32(coef)
+        _flat(g)[:] = _flat(g) * coef
 
 
 class _Event(object):

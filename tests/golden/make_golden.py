@@ -33,11 +33,12 @@ REF_ROOT = os.environ.get("APEX_REFERENCE", "/root/reference")
 
 
 def load_reference():
+    # under its own name, so that objects it pickles carry the real class paths
     spec = importlib.util.spec_from_file_location(
-        "apex_upstream", os.path.join(REF_ROOT, "apex", "__init__.py"),
+        "apex", os.path.join(REF_ROOT, "apex", "__init__.py"),
         submodule_search_locations=[os.path.join(REF_ROOT, "apex")])
     mod = importlib.util.module_from_spec(spec)
-    sys.modules["apex_upstream"] = mod
+    sys.modules["apex"] = mod
     spec.loader.exec_module(mod)
     return mod
 
@@ -328,8 +329,43 @@ def golden_ddp_layout(apex, out):
     dist.destroy_process_group()
 
 
+def golden_checkpoint(apex):
+    """A checkpoint written by the reference: FP16_Optimizer.state_dict() through torch.save
+    (examples/FP16_Optimizer_simple/save_load.py:27-37).  It pickles the DynamicLossScaler object."""
+    shapes, init = make_mlp_case(11)
+    params = [torch.nn.Parameter(p.clone()) for p in init[:4]]
+    inner = torch.optim.SGD(params, lr=0.1, momentum=0.9)
+    with cuda_type_names(), contextlib.redirect_stdout(io.StringIO()):
+        opt = apex.fp16_utils.FP16_Optimizer(inner, dynamic_loss_scale=True,
+                                              dynamic_loss_args={"init_scale": 2**10, "scale_window": 3}, verbose=False)
+    gen = torch.Generator().manual_seed(77)
+    grads = []
+    for it in range(7):
+        gs = [(torch.randn(p.shape, generator=gen) * 0.5).half() for p in params]
+        if it == 2:
+            gs[1][0] = float("inf")
+        grads.append(gs)
+    with contextlib.redirect_stdout(io.StringIO()):
+        for it in range(5):
+            for p, g in zip(params, grads[it]):
+                p.grad = g.clone()
+            opt.update_master_grads()
+            opt.step()
+        ckpt = {"optimizer": opt.state_dict(), "model": [p.data.clone() for p in params]}
+        torch.save(ckpt, os.path.join(HERE, "reference_checkpoint.pt"))
+        for it in range(5, 7):                       # what the reference does after the checkpoint
+            for p, g in zip(params, grads[it]):
+                p.grad = g.clone()
+            opt.update_master_grads()
+            opt.step()
+    torch.save({"grads": grads[5:], "final_masters": [m.data.clone() for m in opt.fp32_from_fp16_groups[0]],
+                "final_model": [p.data.clone() for p in params], "final_scale": float(opt.loss_scale),
+                "final_iter": opt.loss_scaler.cur_iter}, os.path.join(HERE, "reference_checkpoint_after.pt"))
+
+
 def main():
     apex = load_reference()
+    golden_checkpoint(apex)
     out, arrays = {}, {}
     out["torch_version"] = torch.__version__
     golden_scalers(apex, out)

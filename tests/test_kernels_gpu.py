@@ -451,3 +451,55 @@ def test_two_streams_two_threads():
     [x.start() for x in th]
     [x.join() for x in th]
     assert not errs, errs
+
+
+@pytest.mark.parametrize("norm_value,max_norm", [(37.5, 1.0), (0.02, 1.0), (3.0, 0.25)])
+def test_clip_factor_folded_into_fused_step_and_materialisation(norm_value, max_norm):
+    """clip_master_grads as a factor inside the kernels: g * inv_scale * clamp(max_norm/(norm+1e-6), 1)."""
+    grads, masters, models, flags = _step_inputs(12)
+    norm = torch.tensor([norm_value], device=dev())
+    coef = c_oracle.clip_coef(norm_value, max_norm)
+    assert (coef < 1.0) == (max_norm / (norm_value + 1e-6) < 1.0)
+    inv = 1. / 1024
+    # materialisation
+    src = [g for g, f in zip(grads, flags) if f == 0]
+    dst = [torch.zeros(g.numel(), device=dev()) for g in src]
+    _C.mt_grads_to_master(table([src, dst], None, 8192), 0, 1, inv, True, None, (norm, max_norm))
+    for s, d in zip(src, dst):
+        assert np.array_equal(bits(d), c_oracle.f16_to_f32_scaled(bits(s), inv, True, coef))
+        ref = s.float().mul_(inv).mul_(torch.tensor(coef, device=dev()))       # unscale, then clip_grad_norm_'s mul_
+        assert torch.equal(d, ref)
+    # SGD with momentum
+    bufs = [torch.zeros_like(m) for m in masters]
+    o_p = [bits(m).copy() for m in masters]
+    o_b = [np.zeros_like(x) for x in o_p]
+    t = table([grads, masters, bufs, models], None, 2048)
+    for step in range(2):
+        fl = [f | (_C.TF_FIRST_STEP if step == 0 else 0) for f in flags]
+        t.update([grads, masters, bufs, models], fl)
+        _C.mt_fused_sgd(t, 0.1, 0.9, 0.0, 1e-4, False, inv, True, None, (norm, max_norm))
+        for i in range(len(grads)):
+            ns = bool(flags[i] & _C.TF_NO_SCALE)
+            p16 = c_oracle.sgd(bits(grads[i]), o_p[i], o_b[i], 0.1, 0.9, 0.0, 1e-4, False, first=(step == 0),
+                               inv_scale=inv, apply_scale=not ns, clip_coef=None if ns else coef)
+            assert np.array_equal(bits(masters[i]), o_p[i]), (step, i)
+            assert np.array_equal(bits(bufs[i]), o_b[i]), (step, i)
+            if models[i] is not None:
+                assert np.array_equal(bits(models[i]), p16)
+    # Adam
+    grads, masters, models, flags = _step_inputs(13)
+    ms = [torch.zeros_like(m) for m in masters]
+    vs = [torch.zeros_like(m) for m in masters]
+    o_p = [bits(m).copy() for m in masters]
+    o_m = [np.zeros_like(x) for x in o_p]
+    o_v = [np.zeros_like(x) for x in o_p]
+    t5 = table([grads, masters, ms, vs, models], flags, 2048)
+    bc1, bc2 = 1 - 0.9, 1 - 0.999
+    _C.mt_fused_adam(t5, 1e-3, 0.9, 0.999, 1e-8, 0.0, (1e-3 / bc1) * -1, bc2 ** 0.5, False, inv, True, None,
+                     (norm, max_norm))
+    for i in range(len(grads)):
+        ns = bool(flags[i] & _C.TF_NO_SCALE)
+        c_oracle.adam(bits(grads[i]), o_p[i], o_m[i], o_v[i], 1e-3, 0.9, 0.999, 1e-8, 0.0, 1, inv_scale=inv,
+                      apply_scale=not ns, clip_coef=None if ns else coef)
+        assert np.array_equal(bits(masters[i]), o_p[i]) and np.array_equal(bits(ms[i]), o_m[i])
+        assert np.array_equal(bits(vs[i]), o_v[i])
