@@ -81,6 +81,7 @@ SIGNATURES = {
     "apex_b200_mt_l2norm": (_i, [_tp, _i, _d, _i, _vp, ctypes.c_int64, _vp, _vp]),
     "apex_b200_mt_l2norm_noalloc": (_i, [_tp, _i, _d, _i, _vp, _vp]),
     "apex_b200_mt_clip_by_norm": (_i, [_tp, _i, _vp, _d, _vp, _vp]),
+    "apex_b200_mt_larc": (_i, [_tp, _i, _i, _d, _d, _d, _d, _i, _vp, ctypes.c_int64, _vp, _vp]),
 }
 
 
@@ -276,3 +277,12 @@ def mt_clip_by_norm(table, grad_list, norm, max_norm, flag, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_clip_by_norm(table.ref, grad_list, _ptr(norm), float(max_norm), _ptr(flag),
                                          current_stream() if stream is None else stream), "mt_clip_by_norm")
+
+
+def mt_larc(table, grad_list, param_list, trust_coefficient, eps, weight_decay, lr, clip, scratch, norms=None,
+            stream=None):
+    global launches
+    launches += 4 if table.struct.total_chunks > 0 else 1
+    _check(lib.apex_b200_mt_larc(table.ref, grad_list, param_list, float(trust_coefficient), float(eps),
+                                 float(weight_decay), float(lr), int(bool(clip)), _ptr(scratch), scratch.numel(),
+                                 _ptr(norms), current_stream() if stream is None else stream), "mt_larc")

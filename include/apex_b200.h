@@ -291,6 +291,22 @@ int apex_b200_mt_clip_by_norm(const apex_b200_mt_table* t, int grad_list,
                               const float* d_norm, double max_norm,
                               const int32_t* d_flag, void* stream);
 
+/* ---- LARC ---------------------------------------------------------------- */
+
+/* Replaces the per-tensor loop of LARC.step (apex/parallel/LARC.py:68-97) for one
+ * param group: norms of every parameter and gradient, the adaptive rate
+ * trust * |p| / (|g| + |p| * wd + eps) (divided by lr and clamped to 1 when clip != 0),
+ * and g = (g + wd * p) * rate, for all tensors at once and without any host read
+ * (the reference reads two norms per tensor back to compare them with 0; a tensor
+ * with a zero norm is left untouched here too).  Tensors are fp32 where
+ * TF_GRAD_F32 is set, else fp16 (gradient and parameter share the dtype).
+ * d_scratch: >= 2 * total_chunks + n_tensors floats, caller-allocated.
+ * d_norms: optional output, [n_tensors][2] = (|p|, |g|). */
+int apex_b200_mt_larc(const apex_b200_mt_table* t, int grad_list, int param_list,
+                      double trust_coefficient, double eps, double weight_decay,
+                      double lr, int clip, float* d_scratch, int64_t scratch_len,
+                      float* d_norms, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -279,3 +279,22 @@ def dispatch_order(ready_sequence, sizes):
             else:
                 parked.add(b)
     return issued
+
+
+# ---- LARC -------------------------------------------------------------------------------------
+
+def larc_rescale(params, lr, weight_decay, trust_coefficient=0.02, clip=True, eps=1e-8):
+    """The gradient rewrite of LARC.step for one param group (apex/parallel/LARC.py:75-92), in place.
+    ``params``: tensors with ``.grad``."""
+    with torch.no_grad():
+        for p in params:
+            if p.grad is None:
+                continue
+            param_norm = torch.norm(p.data)
+            grad_norm = torch.norm(p.grad.data)
+            if param_norm != 0 and grad_norm != 0:
+                adaptive_lr = trust_coefficient * (param_norm) / (grad_norm + param_norm * weight_decay + eps)
+                if clip:
+                    adaptive_lr = min(adaptive_lr / lr, 1)
+                p.grad.data += weight_decay * p.data
+                p.grad.data *= adaptive_lr

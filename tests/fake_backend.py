@@ -235,7 +235,7 @@ def install(monkeypatch):
     monkeypatch.setattr(_C, "keep_table_refs", True, raising=False)
     for name in ("flag_clear", "mt_check_overflow", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
                  "mt_copy", "mt_zero", "mt_fused_sgd", "mt_fused_adam", "mt_flatten", "mt_scale_unflatten",
-                 "scale_flat", "mt_l2norm", "mt_clip_by_norm"):
+                 "scale_flat", "mt_l2norm", "mt_clip_by_norm", "mt_larc"):
         monkeypatch.setattr(_C, name, globals()[name])
     monkeypatch.setattr(torch.cuda, "Event", _Event)
     monkeypatch.setattr(torch.cuda, "Stream", _Stream)
@@ -243,3 +243,27 @@ def install(monkeypatch):
     monkeypatch.setattr(torch.cuda, "stream", lambda s: contextlib.nullcontext())
     # FP16_Optimizer and DistributedDataParallel gate on 'torch.cuda.*Tensor' strings, as the reference does
     monkeypatch.setattr(torch.Tensor, "type", _cuda_named_type)
+
+
+def mt_larc(table, grad_list, param_list, trust_coefficient, eps, weight_decay, lr, clip, scratch, norms=None,
+            stream=None):
+    """fp32 arithmetic in the order of apex_b200/csrc/mt_larc.cu (norms accumulated in double)."""
+    calls.append("larc")
+    f32 = np.float32
+    for g, p in zip(table.lists[grad_list], table.lists[param_list]):
+        gf = g.detach().float().numpy().reshape(-1)
+        pf = p.detach().float().numpy().reshape(-1)
+        gn = f32(np.sqrt(np.sum(gf.astype(np.float64) ** 2)))
+        pn = f32(np.sqrt(np.sum(pf.astype(np.float64) ** 2)))
+        if pn == 0 or gn == 0:
+            continue
+        r = f32(f32(trust_coefficient) * pn) / f32(f32(gn + f32(pn * f32(weight_decay))) + f32(eps))
+        if clip:
+            r = min(f32(r / f32(lr)), f32(1.0))
+        if g.dtype == torch.float32:
+            out = f32(f32(gf + f32(f32(weight_decay) * pf)) * r)
+            _flat(g)[:] = out
+        else:
+            wp = (f32(weight_decay) * pf).astype(np.float16)
+            s = (gf + wp.astype(np.float32)).astype(np.float16)
+            _flat(g)[:] = (s.astype(np.float32) * r).astype(np.float16).view(np.uint16)

@@ -110,7 +110,7 @@ def _install_double():
     _C.keep_table_refs = True
     for name in ("flag_clear", "mt_check_overflow", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
                  "mt_copy", "mt_zero", "mt_fused_sgd", "mt_fused_adam", "mt_flatten", "mt_scale_unflatten",
-                 "scale_flat", "mt_l2norm", "mt_clip_by_norm"):
+                 "scale_flat", "mt_l2norm", "mt_clip_by_norm", "mt_larc"):
         setattr(_C, name, getattr(fb, name))
     torch.cuda.Event = fb._Event
     torch.cuda.Stream = fb._Stream

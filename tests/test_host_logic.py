@@ -502,3 +502,36 @@ def test_clip_is_virtual_until_somebody_looks(cpu_backend):
     # other norm types go to torch as in the reference
     opt.update_master_grads()
     assert float(opt.clip_master_grads(1e9, norm_type=float("inf"))) == pytest.approx(1 / 64.)
+
+
+@pytest.mark.parametrize("clip", [True, False])
+def test_larc_matches_reference_loop(clip, cpu_backend):
+    from apex_b200.parallel import LARC
+    from oracle import apex_ref
+    torch.manual_seed(9)
+    shapes = [(40, 7), (13,), (5, 5, 3), (1,)]
+    init = [torch.randn(s) * 0.3 for s in shapes]
+    init[3].zero_()                                     # zero parameter norm: the reference skips it
+    ps = [torch.nn.Parameter(t.clone()) for t in init]
+    rs = [torch.nn.Parameter(t.clone()) for t in init]
+    opt = LARC(torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=5e-4), trust_coefficient=0.02, clip=clip)
+    ropt = torch.optim.SGD(rs, lr=0.1, momentum=0.9, weight_decay=5e-4)
+    for it in range(4):
+        for p, r in zip(ps, rs):
+            g = torch.randn(p.shape) * (10.0 if it % 2 else 0.01)
+            p.grad, r.grad = g.clone(), g.clone()
+        if it == 2:
+            ps[1].grad, rs[1].grad = None, None         # parameter without gradient
+        opt.step()
+        apex_ref.larc_rescale(rs, 0.1, 5e-4, 0.02, clip)     # LARC.py:75-92 ...
+        saved = ropt.param_groups[0]['weight_decay']
+        ropt.param_groups[0]['weight_decay'] = 0             # ... with the weight decay absorbed (:73-74, :95-97)
+        ropt.step()
+        ropt.param_groups[0]['weight_decay'] = saved
+        assert opt.optim.param_groups[0]['weight_decay'] == 5e-4      # handed back after the step
+        for p, r in zip(ps, rs):
+            if r.grad is not None:
+                assert torch.allclose(p.grad, r.grad, rtol=2e-6, atol=0)
+            assert torch.allclose(p.data, r.data, rtol=2e-6, atol=1e-9)
+    assert cpu_backend.calls.count("larc") == 4
+    assert repr(opt) == repr(opt.optim) and opt.state_dict().keys() == ropt.state_dict().keys()

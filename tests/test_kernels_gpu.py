@@ -503,3 +503,32 @@ def test_clip_factor_folded_into_fused_step_and_materialisation(norm_value, max_
                       apply_scale=not ns, clip_coef=None if ns else coef)
         assert np.array_equal(bits(masters[i]), o_p[i]) and np.array_equal(bits(ms[i]), o_m[i])
         assert np.array_equal(bits(vs[i]), o_v[i])
+
+
+@pytest.mark.parametrize("clip", [True, False])
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16])
+def test_larc_kernels_against_the_reference_loop_on_gpu(clip, dtype):
+    from apex_b200.multi_tensor import TensorTable, CHUNK_NORM
+    from oracle import apex_ref
+    g = gen(14)
+    sizes = [1, 7, 2048, 70001, 300000, 64, 0, 33]
+    params = [(torch.randn(n, generator=g, device=dev()) * 0.3).to(dtype) for n in sizes]
+    params[5].zero_()                                         # |p| == 0: left alone
+    grads = [(torch.randn(n, generator=g, device=dev()) * (5.0 if i % 2 else 0.02)).to(dtype)
+             for i, n in enumerate(sizes)]
+    grads[3].zero_()                                          # |g| == 0: left alone
+    ref = [torch.nn.Parameter(p.clone()) for p in params]
+    for r, gr in zip(ref, grads):
+        r.grad = gr.clone()
+    apex_ref.larc_rescale(ref, 0.1, 5e-4, 0.02, clip)
+    t = TensorTable(dev(), 2, CHUNK_NORM)
+    t.update([grads, params], [_C.TF_GRAD_F32 if dtype == torch.float32 else 0] * len(sizes))
+    scratch = torch.empty(2 * t.struct.total_chunks + len(sizes), device=dev())
+    norms = torch.zeros(len(sizes), 2, device=dev())
+    _C.mt_larc(t, 0, 1, 0.02, 1e-8, 5e-4, 0.1, clip, scratch, norms)
+    for i, (mine, r, p) in enumerate(zip(grads, ref, params)):
+        if sizes[i]:
+            assert float(norms[i, 0]) == pytest.approx(float(torch.norm(p.float())), rel=3e-6)
+        tol = 3e-6 if dtype == torch.float32 else 2e-3         # fp16: one more rounding of the rate's effect
+        assert torch.allclose(mine.float(), r.grad.float(), rtol=tol, atol=1e-8 if dtype == torch.float32 else 1e-6), i
+    assert torch.equal(grads[5], ref[5].grad) and torch.equal(grads[3], ref[3].grad)
