@@ -198,6 +198,47 @@ def cpu_reference_run(shapes, steps, warmup, budget_s, seed=1234, kind="adam"):
     return total / best, info
 
 
+def gpu_reference_composition(shapes, fp32_mask, kind, dev, steps=3):
+    """The reference's own composition of stock torch ops ON THE GPU (what apex runs there today, the
+    honest "before"): per-tensor `float(x.float().sum())` overflow test with a host sync each
+    (apex/fp16_utils/loss_scaler.py:84-110), per-tensor copy_ and mul_ (fp16util.py:106-112,
+    fp16_optimizer.py:236-241), torch.optim step (:380), per-tensor copy_ back (fp16util.py:127-129).
+    Written out here with plain torch calls; reported next to our number, never used by it."""
+    gen = torch.Generator(device=dev).manual_seed(1234)
+    params = [torch.randn(s, generator=gen, device=dev) * 0.02 if f else
+              (torch.randn(s, generator=gen, device=dev) * 0.02).half() for s, f in zip(shapes, fp32_mask)]
+    grads = [(torch.randn(s, generator=gen, device=dev) * (1e-3 * 65536)).to(p.dtype) for s, p in zip(shapes, params)]
+    masters = [p.detach().clone().float().requires_grad_(True) for p in params]
+    opt = make_optimizer(kind)(masters)
+    inv = 1. / 65536.0
+
+    def one():
+        for g in grads:                                   # has_overflow: a sync per tensor
+            s = float(g.float().sum())
+            if s == float("inf") or s == -float("inf") or s != s:
+                return
+        for m, g in zip(masters, grads):
+            if m.grad is None:
+                m.grad = torch.empty_like(m)
+            m.grad.copy_(g)
+        for m in masters:
+            m.grad.mul_(inv)
+        opt.step()
+        for p, m in zip(params, masters):
+            p.copy_(m)
+    for _ in range(2):
+        one()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        one()
+    torch.cuda.synchronize()
+    ms = (time.perf_counter() - t0) / steps * 1e3
+    del opt, masters, grads, params
+    torch.cuda.empty_cache()
+    return ms
+
+
 def run_reference_arm(args, shapes):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -273,6 +314,7 @@ def main():
     ap.add_argument("--bucket-mb", type=float, default=256.0, help="DDP bucket size for N > 1 (fp16 bytes)")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-gpu-reference", action="store_true")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3)
     shapes = WORKLOADS[args.workload][0]
@@ -440,6 +482,15 @@ def main():
                "api": "param.grad.copy_(pinned host) ; FP16_Optimizer.update_master_grads() ; .step() ; .overflow"}
         del host
 
+    gpu_ref = None
+    if world == 1 and not args.no_gpu_reference:
+        try:
+            ms = gpu_reference_composition(shapes, fp32_mask, kind, dev)
+            gpu_ref = {"ms_per_step": ms, "params_per_s": n_params / (ms * 1e-3), "speedup": ms / ms_per_step,
+                       "what": "the reference's composition of stock torch ops on this GPU (per-tensor "
+                               ".float().sum() host syncs, copy_, mul_, torch.optim foreach step, copy_), 3 steps"}
+        except torch.cuda.OutOfMemoryError:
+            gpu_ref = {"unavailable": "out of memory for a second replica"}
     if rank == 0:
         cpu = None
         if world == 1 and not args.no_cpu_baseline:
@@ -455,7 +506,8 @@ def main():
                        "params": n_params, "tensors": len(shapes), "parallelism": "dp%d" % world,
                        "bucket_mb": args.bucket_mb if world > 1 else None, "buckets": len(buckets),
                        "l2": "no flush: %.1f GB touched per step vs 126 MB L2" % ((bpp + 2) * n_params / 1e9)},
-            "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+            "roofline": roofline, "cpu_baseline": cpu, "reference_composition_on_gpu": gpu_ref, "e2e": e2e,
+            "gpu_launches": launches, "clocks": clocks,
             "breakdown_ms": {"check_overflow": check_ms, "fused_update": fused_ms, "bucket_allreduce_path": comm_ms,
                              "host_python_per_step": host_ms_per_step},
             "hbm_gbs_step": (bpp + 2) * n_params / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,

@@ -1,0 +1,34 @@
+"""bench.py's CPU-only arm (`--impl reference`) prints one well-formed JSON line."""
+import json
+import os
+import subprocess
+import sys
+
+from tests.conftest import ROOT
+
+
+def test_reference_arm_prints_one_json_line():
+    out = subprocess.check_output([sys.executable, os.path.join(ROOT, "bench.py"), "--impl", "reference",
+                                   "--workload", "mlp", "--steps", "3", "--warmup", "1"],
+                                  stderr=subprocess.DEVNULL, timeout=300).decode().strip().splitlines()
+    assert len(out) == 1
+    line = json.loads(out[0])
+    assert line["impl"] == "reference" and line["metric"] == "fused_mp_step_throughput"
+    assert line["unit"] == "params/s" and line["value"] > 0 and line["higher_is_better"] is True
+    assert line["cpu_baseline"]["kind"] == "port" and line["cpu_baseline"]["cores"] >= 1
+    assert line["cpu_baseline"]["value"] == line["value"] == line["e2e"]["value"]
+    assert line["e2e"]["h2d_bytes_per_step"] == 0 and line["e2e"]["d2h_bytes_per_step"] == 0
+    assert "mlp" in line["config"]["workload"] and line["gpu_launches"] == 0
+
+
+def test_workload_shapes_match_the_survey():
+    sys.path.insert(0, ROOT)
+    import bench
+    xl = bench.WORKLOADS["gpt2-xl"][0]
+    assert len(xl) == 580 and sum(bench.numel(s) for s in xl) == 1557611200
+    med = bench.WORKLOADS["gpt2-medium"][0]
+    assert len(med) == 292 and sum(bench.numel(s) for s in med) == 354823168
+    rn = bench.resnet50_shapes()
+    assert len(rn) == 161 and sum(bench.numel(s) for s, _ in rn) == 25557032
+    assert sum(1 for _, f in rn if f) == 106 and sum(bench.numel(s) for s, f in rn if f) == 53120
+    assert sum(bench.numel(s) for s in bench.WORKLOADS["mlp"][0]) == 8393728

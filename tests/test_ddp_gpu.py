@@ -131,6 +131,37 @@ def _worker(rank, world, port, out_dir):
     big = torch.full((1000,), 40000.0, device="cuda").half()
     flat_dist_call([big, big.clone()], dist.all_reduce)
     ok["fp16_overflow_stays_inf"] = bool(torch.isinf(big).all())
+    # a real model through DistributedDataParallel: learning iteration (flat call per dtype), then
+    # overlapped iterations whose multi-tensor buckets go through the symmetric-memory pipeline;
+    # gradients must equal the mean of the ranks' local gradients, with fresh .grad tensors every time
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.ReLU(), torch.nn.Linear(256, 256), torch.nn.ReLU(),
+                              torch.nn.Linear(256, 10)).cuda()
+    twin = torch.nn.Sequential(torch.nn.Linear(64, 256), torch.nn.ReLU(), torch.nn.Linear(256, 256), torch.nn.ReLU(),
+                               torch.nn.Linear(256, 10)).cuda()
+    twin.load_state_dict(net.state_dict())
+    if rank != 0:
+        for p in net.parameters():
+            p.data.add_(1.0)                   # construction must broadcast rank 0's values
+    ddp = DDP(net, message_size=20000)
+    good = all(torch.equal(p.data, q.data) for p, q in zip(net.parameters(), twin.parameters()))
+    for it in range(5):
+        gg = torch.Generator(device="cuda").manual_seed(1000 * it + rank)
+        xb = torch.randn(32, 64, generator=gg, device="cuda")
+        net.zero_grad(set_to_none=True)
+        twin.zero_grad(set_to_none=True)
+        ddp(xb).pow(2).sum().backward()
+        twin(xb).pow(2).sum().backward()
+        torch.cuda.synchronize()
+        for p, q in zip(net.parameters(), twin.parameters()):
+            want = q.grad.clone()
+            dist.all_reduce(want)
+            want /= world
+            good &= bool(torch.allclose(p.grad, want, rtol=1e-5, atol=1e-6))
+    ok["ddp_real_model"] = bool(good)
+    ok["ddp_real_model_buckets"] = ddp.num_buckets
+    ok["ddp_used_symm"] = any(type(s).__name__ == "SymmSlot" for s in ddp._pipeline.slots.values())
+
     # our own allreduce over symmetric memory (switch multicast if the box has it, and peer-to-peer)
     from apex_b200.parallel import symm
     from apex_b200.parallel.distributed import _BucketPipeline
@@ -183,8 +214,9 @@ def test_two_ranks_nccl(tmp_path):
     mp.spawn(_worker, args=(WORLD, port, str(tmp_path)), nprocs=WORLD, join=True)
     for r in range(WORLD):
         res = torch.load(os.path.join(str(tmp_path), "rank%d.pt" % r), weights_only=False)
-        for key in ("race", "fp16_average", "fp16_overflow_stays_inf", "symm_auto", "symm_p2p",
-                    "symm_auto_overflow", "symm_p2p_overflow"):
+        assert res["ddp_real_model_buckets"] >= 2
+        for key in ("race", "fp16_average", "fp16_overflow_stays_inf", "ddp_real_model", "ddp_used_symm",
+                    "symm_auto", "symm_p2p", "symm_auto_overflow", "symm_p2p_overflow"):
             assert res[key] is True, (key, res)
         print("multicast used:", res["symm_auto_multicast"], "| bits equal to reference composition:",
               res["fp16_same_bits_as_reference_composition"], "| symm default:", res["symm_default_on"])

@@ -328,3 +328,27 @@ def test_config2_gpt2_medium_full_size_properties():
     assert opt.overflow is False
     for p, m in zip(params, masters):
         assert torch.equal(p.data, m.data.half())
+
+
+def test_amp_handle_on_gpu():
+    """apex.amp's scale_loss context (apex/amp/handle.py:32-63) with the two-launch unscale."""
+    from apex_b200.amp import AmpHandle
+    w = torch.nn.Parameter(torch.tensor([1.0, 2.0, 3.0], device=dev()))
+    opt = torch.optim.SGD([w], lr=0.5)
+    handle = AmpHandle()
+    coeff = torch.tensor([1.0, 3.0, -2.0], device=dev())
+    with handle.scale_loss((w * coeff).sum(), opt) as scaled:
+        scaled.backward()
+    assert torch.equal(w.grad, coeff)                       # unscaled in place by 1/2^16: exact
+    opt.step()
+    assert torch.equal(w.data, torch.tensor([0.5, 0.5, 4.0], device=dev()))
+    opt.zero_grad()
+    bad = torch.tensor([float("inf"), 1.0, 1.0], device=dev())
+    with handle.scale_loss((w * bad).sum(), opt) as scaled:
+        scaled.backward()
+    before = w.data.clone()
+    opt.step()                                              # one-shot no-op
+    assert torch.equal(w.data, before) and handle._default_scaler.loss_scale() == 2.**15
+    w.grad = torch.ones(3, device=dev())
+    opt.step()
+    assert torch.equal(w.data, before - 0.5)
