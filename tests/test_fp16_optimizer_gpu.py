@@ -352,3 +352,101 @@ def test_amp_handle_on_gpu():
     w.grad = torch.ones(3, device=dev())
     opt.step()
     assert torch.equal(w.data, before - 0.5)
+
+
+def test_config3_resnet50_full_shapes_against_reference_composition():
+    """All 161 ResNet-50 tensors (55 fp16 + 106 fp32 BatchNorm vectors of 64..2048 elements), SGD with
+    momentum and weight decay, dynamic scaling, overflow injected into fp16 and fp32 gradients."""
+    import bench
+    spec = bench.resnet50_shapes()
+    conv = [s for s, f in spec if not f]
+    bn = [s for s, f in spec if f]
+    assert len(conv) == 55 and len(bn) == 106
+    mine, theirs, opt, ref, g = _make_pair(conv, bn, lambda ps: torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=1e-4),
+                                           41, dynamic_loss_scale=True,
+                                           dynamic_loss_args={"init_scale": 2**15, "scale_window": 3})
+    inject = {1: (54, 999, INF), 4: (55 + 100, 63, NAN), 5: (0, 0, -INF)}
+    _same_run(mine, theirs, opt, ref, g, 10, inject)
+
+
+def test_config4_lstm_full_shapes_with_clipping():
+    """word_language_model LSTM, 135,891,278 fp16 parameters in 11 tensors (vocab 33,278 is not a
+    multiple of 8: ragged tails), backward -> clip_master_grads(0.25) -> step with injected inf/NaN."""
+    V, H = 33278, 1500
+    shapes = [(V, H), (4 * H, H), (4 * H, H), (4 * H,), (4 * H,), (4 * H, H), (4 * H, H), (4 * H,), (4 * H,), (V, H), (V,)]
+    assert sum(int(np.prod(s)) for s in shapes) == 135891278
+    mine, theirs, opt, ref, g = _make_pair(shapes, [], lambda ps: torch.optim.SGD(ps, lr=20.0), 42,
+                                           dynamic_loss_scale=True,
+                                           dynamic_loss_args={"init_scale": 2**14, "scale_window": 4})
+    inject = {2: (10, V - 1, INF), 3: (0, V * H - 3, NAN), 7: (5, 12345, -INF)}
+    _same_run(mine, theirs, opt, ref, g, 10, inject, clip=0.25, exact=False)
+
+
+def test_config5_gpt2_xl_full_size_adam_properties():
+    """1,557,611,200 fp16 params in 580 tensors with Adam (BASELINE config 5 / the bench workload):
+    first step against torch's own kernels tensor by tensor, then skip-on-overflow and the copy invariant."""
+    shapes = gpt2_shapes(48, 1600)
+    assert len(shapes) == 580 and sum(int(np.prod(s)) for s in shapes) == 1557611200
+    g = gen(43)
+    params = [torch.nn.Parameter((torch.randn(s, generator=g, device=dev()) * 0.02).half()) for s in shapes]
+    opt = FP16_Optimizer(torch.optim.Adam(params, lr=1e-3), dynamic_loss_scale=True,
+                         dynamic_loss_args={"init_scale": 2.0**16}, verbose=False)
+    masters = opt.fp32_from_fp16_groups[0]
+    grads = [(torch.randn(p.shape, generator=g, device=dev()) * (1e-3 * 65536)).half() for p in params]
+    for p, gr in zip(params, grads):
+        p.grad = gr
+    # reference composition for a sample of tensors (first, last, big, small, middle), computed BEFORE the step
+    sample = [0, 1, 2, 5, 301, 578, 579]
+    want = {}
+    for i in sample:
+        q = torch.nn.Parameter(masters[i].data.clone())
+        q.grad = grads[i].float().mul_(1. / 65536)
+        topt = torch.optim.Adam([q], lr=1e-3, foreach=True)
+        topt.step()
+        want[i] = (q.data, topt.state[q]["exp_avg"], topt.state[q]["exp_avg_sq"])
+    opt.update_master_grads()
+    opt.step()
+    assert opt.overflow is False
+    for i in sample:
+        st = opt.optimizer.state[masters[i]]
+        assert torch.equal(masters[i].data, want[i][0]), i
+        assert torch.equal(st["exp_avg"], want[i][1]) and torch.equal(st["exp_avg_sq"], want[i][2]), i
+        assert float(st["step"]) == 1.0
+    for p, m in zip(params, masters):
+        assert torch.equal(p.data, m.data.half())
+    del want
+    # overflow in the very last element: nothing moves, the step counters stay
+    sums = [float(masters[i].data.double().sum()) for i in sample]
+    grads[-1].view(-1)[-1] = NAN
+    opt.update_master_grads()
+    with contextlib.redirect_stdout(io.StringIO()):
+        opt.step()
+    assert opt.overflow is True and opt.loss_scale == 2.0**15
+    assert [float(masters[i].data.double().sum()) for i in sample] == sums
+    assert float(opt.optimizer.state[masters[0]]["step"]) == 1.0
+    grads[-1].view(-1)[-1] = 0.0
+    opt.update_master_grads()
+    opt.step()
+    assert opt.overflow is False and float(opt.optimizer.state[masters[579]]["step"]) == 2.0
+
+
+def test_closure_retries_while_the_gradients_overflow():
+    """_step_with_closure (apex/fp16_utils/fp16_optimizer.py:386-423): the closure is run again, with
+    a smaller scale each time, until its gradients are finite."""
+    p = torch.nn.Parameter(torch.ones(1000, device=dev()).half())
+    opt = FP16_Optimizer(torch.optim.SGD([p], lr=0.25), dynamic_loss_scale=True,
+                         dynamic_loss_args={"init_scale": 2.0**18}, verbose=False)
+    seen = []
+
+    def closure():
+        seen.append(float(opt.loss_scale))
+        g = torch.full((1000,), 0.5 * float(opt.loss_scale), device=dev())      # "scaled" gradient of 0.5
+        p.grad = g.half()                                                          # inf in fp16 above 2^17 * 0.5
+        opt.update_master_grads()
+        return torch.tensor(1.0)
+    with contextlib.redirect_stdout(io.StringIO()) as out:
+        opt.step(closure)
+    assert seen == [2.0**18, 2.0**17, 2.0**16]
+    assert out.getvalue().count("OVERFLOW within closure! Skipping step.") == 2
+    assert torch.equal(p.data, torch.full((1000,), 0.875, device=dev()).half())
+    assert opt.first_closure_call_this_step is True
