@@ -732,6 +732,8 @@ class FP16_Optimizer(object):
         inv_scale, apply_scale = (1.0, False) if from_masters else pending
         clip = None if from_masters else self._clip
         plans = []
+        if len(self.optimizer.param_groups) != len(self.fp16_groups):
+            return None           # a group was added after wrapping: the inner optimizer handles it
         for gi, group in enumerate(self.optimizer.param_groups):
             plan = self._plan_for(kind, gi, group, from_masters)
             if plan is False:
@@ -819,7 +821,16 @@ class FP16_Optimizer(object):
             return          # overflow already known on the host (custom scaler path)
         # fp32-native parameters are the user's own tensors: unscale in place now.
         if apply_scale:
-            grads = [p.grad for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
+            groups = self.optimizer.param_groups
+            if len(groups) == len(self.fp16_groups) and all(
+                    len(g['params']) == len(h) + len(f)
+                    for g, h, f in zip(groups, self.fp16_groups, self.fp32_from_fp32_groups)):
+                grads = [p.grad for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
+            else:
+                # param_groups were edited after wrapping: the reference unscales the gradient of
+                # EVERY parameter the inner optimizer owns (:236-241); masters are handled virtually
+                grads = [p.grad for g in groups for p in g['params']
+                         if type(p) is not _MasterParam and p.grad is not None]
             self._unscale_in_place(grads, inv_scale, flag)
         self._pending = (inv_scale, apply_scale)
 

@@ -535,3 +535,48 @@ def test_larc_matches_reference_loop(clip, cpu_backend):
             assert torch.allclose(p.data, r.data, rtol=2e-6, atol=1e-9)
     assert cpu_backend.calls.count("larc") == 4
     assert repr(opt) == repr(opt.optim) and opt.state_dict().keys() == ropt.state_dict().keys()
+
+
+def test_two_param_groups_with_their_own_hyperparameters(cpu_backend):
+    from apex_b200.fp16_utils import FP16_Optimizer
+    from oracle import apex_ref
+    torch.manual_seed(11)
+    a = [(torch.randn(50) * 0.1).half(), (torch.randn(6, 6) * 0.1).half()]
+    b = [(torch.randn(17) * 0.1).half(), torch.randn(9) * 0.1]
+
+    def make(pa, pb):
+        return torch.optim.SGD([{"params": pa, "lr": 0.5, "momentum": 0.9},
+                                {"params": pb, "lr": 0.05, "momentum": 0.0, "weight_decay": 0.01}], lr=1.0)
+    pa, pb = [torch.nn.Parameter(t.clone()) for t in a], [torch.nn.Parameter(t.clone()) for t in b]
+    ra, rb = [torch.nn.Parameter(t.clone()) for t in a], [torch.nn.Parameter(t.clone()) for t in b]
+    opt = FP16_Optimizer(make(pa, pb), static_loss_scale=16.0, verbose=False)
+    assert len(opt.fp16_groups) == 2 and len(opt.fp32_from_fp32_groups[1]) == 1
+
+    class Ref(apex_ref.MixedPrecisionStep):       # same composition, two groups
+        pass
+    # the restatement takes one flat list; build its optimizer with the same two groups
+    ref = apex_ref.MixedPrecisionStep(ra + rb, lambda owned: make(owned[:2], owned[2:]), static_loss_scale=16.0)
+    for it in range(4):
+        for p, r in zip(pa + pb, ra + rb):
+            g = (torch.randn(p.shape) * 16).to(p.dtype)
+            p.grad, r.grad = g.clone(), g.clone()
+        if it == 2:
+            opt.param_groups[0]["lr"] = 0.25               # schedulers edit the group dicts in place
+            ref.optimizer.param_groups[0]["lr"] = 0.25
+        opt.update_master_grads()
+        opt.step()
+        ref.update_master_grads()
+        ref.step()
+    assert cpu_backend.calls.count("fused_sgd") == 8        # one launch per group per step
+    for m, rm in zip(opt.fp32_from_fp16_groups[0] + opt.fp32_from_fp16_groups[1], ref.masters):
+        assert torch.equal(m.data, rm.data)
+    assert torch.equal(pb[1].data, rb[1].data)
+    # a group added after wrapping is left to the inner optimizer (generic path), as in the reference
+    extra = torch.nn.Parameter(torch.ones(4))
+    opt.optimizer.add_param_group({"params": [extra]})
+    extra.grad = torch.ones(4)
+    for p in pa + pb:
+        p.grad = torch.zeros_like(p)
+    opt.update_master_grads()
+    opt.step()
+    assert torch.allclose(extra.data, torch.full((4,), 1.0 - 1.0 / 16))   # lr 1.0, its gradient was unscaled too
