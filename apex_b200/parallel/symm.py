@@ -49,18 +49,56 @@ def mark_broken(err):
     warnings.warn("apex_b200: symmetric-memory allreduce unavailable (%s); using NCCL" % (err,))
 
 
+class _Arena(object):
+    """One symmetric-memory allocation that many buckets are carved out of: a single rendezvous
+    (collective, milliseconds) serves hundreds of buckets.  Sizes double, so a model needs a handful."""
+
+    MIN_BYTES = 64 << 20
+    ALIGN = 256
+
+    def __init__(self, nbytes, device):
+        import torch.distributed._symmetric_memory as symm_mem
+        self.nbytes = nbytes
+        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.buf.zero_()
+        self.handle = symm_mem.rendezvous(self.buf, dist.group.WORLD)      # same order on every rank
+        self.used = 0
+
+    def take(self, nbytes):
+        start = (self.used + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        if start + nbytes > self.nbytes:
+            return None
+        self.used = start + nbytes
+        return start
+
+
+_arenas = {}      # device index -> list of arenas (buckets of every DDP instance of the process share them)
+
+
+def _carve(nbytes, device):
+    arenas = _arenas.setdefault(device.index, [])
+    for arena in arenas:
+        off = arena.take(nbytes)
+        if off is not None:
+            return arena, off
+    size = max(_Arena.MIN_BYTES, nbytes, 2 * arenas[-1].nbytes if arenas else 0)
+    arena = _Arena(size, device)
+    arenas.append(arena)
+    return arena, arena.take(nbytes)
+
+
 class SymmSlot(object):
     """A flat bucket living in symmetric memory + the table of the tensors it stands for."""
 
     def __init__(self):
         self.table = None
-        self.flat = None          # symmetric tensor, padded
+        self.flat = None          # padded slice of an arena, typed
         self.view = None          # first `total` elements
         self.handle = None
+        self.offset = 0           # byte offset of the slice inside the arena
         self.total = 0
 
     def bind(self, tensors):
-        import torch.distributed._symmetric_memory as symm_mem
         head = tensors[0]
         if head.dtype not in (torch.float16, torch.float32):
             raise TypeError("apex_b200: symmetric-memory buckets are fp16 or fp32")
@@ -73,10 +111,10 @@ class SymmSlot(object):
         if self.flat is None or total != self.total or self.flat.dtype != head.dtype:
             unit = (16 // head.element_size()) * world
             padded = (total + unit - 1) // unit * unit
-            group = dist.group.WORLD
-            self.flat = symm_mem.empty(padded, dtype=head.dtype, device=head.device)
-            self.flat.zero_()
-            self.handle = symm_mem.rendezvous(self.flat, group)       # collective: same order on every rank
+            arena, off = _carve(padded * head.element_size(), head.device)
+            self.flat = arena.buf[off:off + padded * head.element_size()].view(head.dtype)
+            self.handle = arena.handle
+            self.offset = off
             self.view = self.flat[:total]
             self.total = total
         if self.table is None:
@@ -93,7 +131,8 @@ class SymmSlot(object):
         mc = int(h.multicast_ptr or 0)
         use_mc = mc != 0 and not _force_p2p and (_force_mc or h.world_size > 2)
         ctas = _ctas if _ctas > 0 else (32 if use_mc else 148)
-        _C.symm_allreduce(list(h.buffer_ptrs), mc if use_mc else 0, h.rank, h.world_size, self.flat.numel(),
+        peers = [int(p) + self.offset for p in h.buffer_ptrs]
+        _C.symm_allreduce(peers, mc + self.offset if use_mc else 0, h.rank, h.world_size, self.flat.numel(),
                           self.flat.dtype, ctas)
 
     def allreduce(self):

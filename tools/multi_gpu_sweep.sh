@@ -20,6 +20,10 @@ PY
     echo "$TAG FAILED"; tail -5 gpurun_out/sweep_last.err
   fi
 }
+if [ -n "$BUCKETS" ]; then
+  for mb in $BUCKETS; do TAG=${SWEEPTAG:-auto} run $mb; done
+  exit 0
+fi
 if [ "$QUICK" = "3" ]; then
   TAG=auto run 256; TAG=auto run 1024; TAG=auto run 64
   APEX_B200_SYMM_CTAS=64 TAG=auto_ctas64 run 256
