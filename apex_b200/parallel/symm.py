@@ -142,48 +142,46 @@ class SymmSlot(object):
 
 
 class SymmPipeline(object):
-    """gather / allreduce / scatter of consecutive buckets on three streams with ONE cross-rank
-    barrier per bucket: the barrier that tells rank r "every rank has gathered bucket b" is enqueued
-    by every rank after its allreduce of bucket b-1, so it also tells "bucket b-1 is complete
-    everywhere" and releases the scatter of b-1.  ``flush`` adds the barrier for the last bucket."""
+    """gather / allreduce / scatter of consecutive buckets overlapped.
+
+    Buckets alternate between two collective streams.  On its stream a bucket runs
+        wait(gathered) -> barrier "every rank has gathered b" -> allreduce kernel -> barrier "every rank
+        has reduced b" -> event for the scatter
+    so the barriers of bucket b+1 (tiny kernels that spin until all ranks arrive) execute while the
+    allreduce kernel of bucket b is still moving data: the NVLink-bound kernels run back to back
+    instead of being separated by a cross-rank round trip.  Barriers in flight at the same time use
+    different signal-pad channels (2 per stream).  The allreduce kernels never wait for a peer, so
+    there is no circular wait.  APEX_B200_SYMM_STREAMS=1 serialises everything on one stream."""
 
     def __init__(self, gather_stream, scatter_stream):
         self.gather_stream = gather_stream
         self.scatter_stream = scatter_stream
-        self.comm_stream = torch.cuda.Stream()
-        self.waiting = None          # (slot, view, flag) whose allreduce is enqueued but not yet certified
-
-    def _release(self, slot_for_barrier):
-        """On the comm stream: barrier, then let the scatter of the waiting bucket go."""
-        slot_for_barrier.barrier(0)
-        if self.waiting is not None:
-            slot, view, flag = self.waiting
-            self.waiting = None
-            done = torch.cuda.Event()
-            done.record()
-            with torch.cuda.stream(self.scatter_stream):
-                self.scatter_stream.wait_event(done)
-                _C.mt_scale_unflatten(slot.table, view, 0, dist.get_world_size(), True, flag)
+        n = 1 if os.environ.get("APEX_B200_SYMM_STREAMS", "2") == "1" else 2
+        self.comm_streams = [torch.cuda.Stream() for _ in range(n)]
+        self.count = 0
 
     def submit(self, slot, bucket, flag):
         view = slot.bind(bucket)
         _C.mt_flatten(slot.table, 0, view)            # on the gather stream (current)
         gathered = torch.cuda.Event()
         gathered.record()
-        with torch.cuda.stream(self.comm_stream):
-            self.comm_stream.wait_event(gathered)
-            self._release(slot)
+        k = self.count % len(self.comm_streams)
+        self.count += 1
+        cs = self.comm_streams[k]
+        with torch.cuda.stream(cs):
+            cs.wait_event(gathered)
+            slot.barrier(2 * k)
             slot.launch_allreduce()
-            self.waiting = (slot, view, flag)
-
-    def flush(self):
-        if self.waiting is not None:
-            with torch.cuda.stream(self.comm_stream):
-                self._release(self.waiting[0])
+            slot.barrier(2 * k + 1)
+            reduced = torch.cuda.Event()
+            reduced.record()
+        with torch.cuda.stream(self.scatter_stream):
+            self.scatter_stream.wait_event(reduced)
+            _C.mt_scale_unflatten(slot.table, view, 0, dist.get_world_size(), True, flag)
 
     def join(self, stream):
-        self.flush()
-        stream.wait_stream(self.comm_stream)
+        for cs in self.comm_streams:
+            stream.wait_stream(cs)
 
 
 def average_bucket(slot, bucket, flag=None, comm_stream=None, scatter_stream=None):
