@@ -523,8 +523,11 @@ def main():
                 kernel = {"ms_per_step": k_ms, "launches_per_step": t_ar.count() / args.steps, "algbw_gbs": k_alg,
                           "busbw_gbs": k_alg * 2 * (world - 1) / world,
                           "frac_of_900": k_alg * 2 * (world - 1) / world / 900.0,
-                          "what": "apex_b200_symm_allreduce launches only (CUDA events on their stream); they "
-                                  "overlap the gather/scatter kernels of neighbouring buckets"}
+                          "what": "sum of the durations of the apex_b200_symm_allreduce launches (CUDA events on "
+                                  "their streams).  Consecutive buckets run on two alternating streams, so two "
+                                  "of these kernels (and the gather/scatter of their neighbours) share NVLink and "
+                                  "HBM at a time: the sum can exceed the wall time of the bucket path.  Isolated "
+                                  "kernel rate: tools/allreduce_bench.py (839 GB/s busbw at 1 GiB on 8 GPUs)"}
             line["allreduce"] = {"bytes": s_bytes, "ms": comm_ms, "algbw_gbs": algbw,
                                  "transport": "apex_b200 symmetric-memory two-shot (NVSwitch multimem beyond 2 "
                                               "ranks, peer-to-peer at 2)" if _symm.enabled() else "NCCL",
