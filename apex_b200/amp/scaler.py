@@ -12,7 +12,7 @@ value, two launches instead of 3n.
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_ZERO, new_flag
+from ..multi_tensor import TensorTable, CHUNK_ZERO, new_flag, is_dense
 
 
 def _flags_for(grads):
@@ -24,8 +24,8 @@ def _flags_for(grads):
             flags.append(0)
         else:
             raise TypeError("apex_b200.amp: gradients must be fp16 or fp32, got %s" % g.dtype)
-        if not g.is_contiguous():
-            raise RuntimeError("apex_b200.amp: gradients must be contiguous")
+        if not is_dense(g):
+            raise RuntimeError("apex_b200.amp: gradients must be dense (contiguous or channels-last)")
     return flags
 
 

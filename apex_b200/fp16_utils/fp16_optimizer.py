@@ -35,7 +35,7 @@ import torch
 
 from .. import _C
 from ..multi_tensor import (TensorTable, CHUNK_STEP, CHUNK_STREAM, CHUNK_CHECK, CHUNK_ZERO, CHUNK_NORM,
-                            new_flag, same_objects)
+                            new_flag, same_objects, is_dense, same_layout)
 from .loss_scaler import DynamicLossScaler, LossScaler
 from .fp16util import master_params_to_model_params, clip_grad_norm
 
@@ -116,7 +116,7 @@ class _StepPlan(object):
         n16 = len(halves)
         for i, g in enumerate(grads):
             want = want16 if i < n16 else torch.float32
-            if g is None or g.dtype != want or g.is_sparse or not g.is_contiguous():
+            if g is None or g.dtype != want or g.is_sparse or not is_dense(g):
                 return False
         for model, master in zip(halves, masters):
             params.append(master.data)
@@ -127,8 +127,9 @@ class _StepPlan(object):
             models.append(None)
             # already unscaled in place by update_master_grads, as the reference does
             flags.append(_C.TF_GRAD_F32 | _C.TF_NO_MODEL | _C.TF_NO_SCALE)
-        for t in params + [m for m in models if m is not None]:
-            if not t.is_contiguous():
+        # elementwise over flat memory: gradient, master and model copy must share one layout
+        for g, pm, md in zip(grads, params, models):
+            if not same_layout((g, pm, md)):
                 return False
         opt._ensure_device(grads[0])
         plan = _StepPlan()
@@ -164,7 +165,7 @@ class _StepPlan(object):
                     buf = torch.empty_like(params[i])
                     fresh.append((p, {'momentum_buffer': buf}))
                     flags[i] |= _C.TF_FIRST_STEP
-                elif buf.dtype != torch.float32 or not buf.is_contiguous():
+                elif buf.dtype != torch.float32 or not same_layout((buf, params[i])):
                     return False
                 bufs.append(buf)
                 held.append((buf,))
@@ -195,8 +196,7 @@ class _StepPlan(object):
             if not isinstance(st['step'], torch.Tensor) or st['step'].is_cuda:
                 return False
             m, v = st['exp_avg'], st['exp_avg_sq']
-            if m.dtype != torch.float32 or v.dtype != torch.float32 or \
-                    not m.is_contiguous() or not v.is_contiguous():
+            if m.dtype != torch.float32 or v.dtype != torch.float32 or not same_layout((m, v, params[i])):
                 return False
             ms.append(m)
             vs.append(v)
@@ -465,8 +465,8 @@ class FP16_Optimizer(object):
         if not table.built_from(grads):
             flags = []
             for g in grads:
-                if not g.is_contiguous():
-                    raise RuntimeError("apex_b200: gradients must be contiguous")
+                if not is_dense(g):
+                    raise RuntimeError("apex_b200: gradients must be dense (contiguous or channels-last)")
                 if g.dtype == torch.float16:
                     flags.append(0)
                 elif g.dtype == torch.float32:
@@ -509,8 +509,8 @@ class FP16_Optimizer(object):
             for model, master in zip(fp16_group, masters):
                 if model.grad is not None:
                     mg = _raw_grad(master)
-                    if mg is None:
-                        mg = torch.empty_like(master.data)
+                    if mg is None or not same_layout((mg, model.grad)):
+                        mg = torch.empty_like(model.grad, dtype=torch.float32)     # the gradient's own layout
                         master.grad = mg
                     srcs.append(model.grad.data)
                     dsts.append(mg.data)
@@ -549,8 +549,8 @@ class FP16_Optimizer(object):
             table = self._unscale_table = TensorTable(self._device, 1, CHUNK_STREAM)
         if not table.built_from(grads):
             for g in grads:
-                if g.dtype != torch.float32 or not g.is_contiguous():
-                    raise RuntimeError("apex_b200: fp32 gradients must be contiguous float tensors")
+                if g.dtype != torch.float32 or not is_dense(g):
+                    raise RuntimeError("apex_b200: fp32 gradients must be dense float tensors")
             table.update([grads], [_C.TF_GRAD_F32] * len(grads))
             table.remember(grads)
         _C.mt_unscale(table, 0, inv_scale, flag, 0)

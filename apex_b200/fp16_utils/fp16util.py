@@ -11,7 +11,7 @@ import torch.nn as nn
 from torch._utils import _flatten_dense_tensors
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STREAM
+from ..multi_tensor import TensorTable, CHUNK_STREAM, same_layout
 
 
 class tofp16(nn.Module):
@@ -96,8 +96,8 @@ def _convert_pairs(srcs, dsts, flag=None, inv_scale=1.0, apply_scale=False):
     """dst[i] <- src[i] for every pair, grouped by (src dtype, dst dtype)."""
     groups = {}
     for s, d in zip(srcs, dsts):
-        if not (s.is_contiguous() and d.is_contiguous()):
-            raise RuntimeError("apex_b200: tensors must be contiguous")
+        if not ((s.is_contiguous() and d.is_contiguous()) or same_layout((s, d))):
+            raise RuntimeError("apex_b200: tensors must be contiguous, or dense with one common layout")
         if s.numel() != d.numel():
             raise RuntimeError("apex_b200: size mismatch between model and master tensor")
         groups.setdefault((s.dtype, d.dtype), ([], []))

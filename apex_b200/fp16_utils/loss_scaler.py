@@ -9,7 +9,7 @@ launch that raises a single device word, and the host reads that word once.
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_CHECK, new_flag
+from ..multi_tensor import TensorTable, CHUNK_CHECK, new_flag, is_dense
 
 
 def to_python_float(t):
@@ -43,8 +43,8 @@ class _OverflowProbe(object):
             self.table = TensorTable(dev, 1, CHUNK_CHECK)
             self.flag = new_flag(dev)
         for g in grads:
-            if not g.is_contiguous():
-                raise RuntimeError("apex_b200: gradients must be contiguous")
+            if not is_dense(g):
+                raise RuntimeError("apex_b200: gradients must be dense (contiguous or channels-last)")
         self.table.update([grads], _grad_flags(grads))
         _C.flag_clear(self.flag)
         _C.mt_check_overflow(self.table, 0, self.flag)

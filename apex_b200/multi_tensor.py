@@ -124,6 +124,35 @@ class TensorTable(object):
         self._refs = None
 
 
+def is_dense(t):
+    """True when the tensor occupies one gap-free block of memory: row-major contiguous, or one of
+    torch's channels-last formats (conv weights and their gradients under channels_last training).
+    Elementwise kernels may then treat it as a flat array -- provided every tensor they combine it
+    with has the same strides (``same_layout``)."""
+    if t.is_contiguous():
+        return True
+    if t.dim() == 4:
+        return t.is_contiguous(memory_format=torch.channels_last)
+    if t.dim() == 5:
+        return t.is_contiguous(memory_format=torch.channels_last_3d)
+    return False
+
+
+def same_layout(tensors):
+    """All tensors (None entries ignored) dense and laid out identically."""
+    first = None
+    for t in tensors:
+        if t is None:
+            continue
+        if not is_dense(t):
+            return False
+        if first is None:
+            first = t
+        elif t.shape != first.shape or t.stride() != first.stride():
+            return False
+    return True
+
+
 def same_objects(a, b):
     """True when two equally long sequences hold identical objects position by position."""
     return len(a) == len(b) and all(map(operator.is_, a, b))

@@ -8,7 +8,7 @@ does it for every tensor without any host read, then the wrapped optimizer steps
 import torch
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_NORM
+from ..multi_tensor import TensorTable, CHUNK_NORM, same_layout
 
 
 class LARC(object):
@@ -55,8 +55,8 @@ class LARC(object):
                 continue
             if g.dtype != p.dtype or p.dtype not in (torch.float16, torch.float32):
                 raise TypeError("apex_b200 LARC: parameters and gradients must both be fp16 or both fp32")
-            if not (g.is_contiguous() and p.is_contiguous()):
-                raise RuntimeError("apex_b200 LARC: tensors must be contiguous")
+            if not same_layout((g, p)):
+                raise RuntimeError("apex_b200 LARC: parameter and gradient must be dense and share a layout")
             grads.append(g)
             params.append(p.data)
             flags.append(_C.TF_GRAD_F32 if p.dtype == torch.float32 else 0)

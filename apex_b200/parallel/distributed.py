@@ -25,7 +25,7 @@ from torch.autograd import Variable
 from torch.nn.modules import Module
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STREAM
+from ..multi_tensor import TensorTable, CHUNK_STREAM, is_dense
 from . import symm
 
 # bucket class per dtype; leftovers are appended in this order (reference :154-156, :178-180)
@@ -54,8 +54,8 @@ class _FlatSlot(object):
             if t.dtype != head.dtype or t.device != head.device:
                 raise TypeError("apply_flat_dist_call needs tensors of one type, got %s and %s"
                                 % (head.type(), t.type()))
-            if not t.is_contiguous():
-                raise RuntimeError("apex_b200: bucket tensors must be contiguous")
+            if not is_dense(t):      # the flat buffer holds each tensor in ITS memory order; the round trip restores it
+                raise RuntimeError("apex_b200: bucket tensors must be dense (contiguous or channels-last)")
             total += t.numel()
         if self.table is None or self.table.device != head.device:
             self.table = TensorTable(head.device, 1, CHUNK_STREAM)

@@ -22,7 +22,7 @@ import torch
 import torch.distributed as dist
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STREAM
+from ..multi_tensor import TensorTable, CHUNK_STREAM, is_dense
 
 _enabled = os.environ.get("APEX_B200_SYMM", "1") != "0"
 _ctas = int(os.environ.get("APEX_B200_SYMM_CTAS", "0"))
@@ -104,8 +104,8 @@ class SymmSlot(object):
             raise TypeError("apex_b200: symmetric-memory buckets are fp16 or fp32")
         total = 0
         for t in tensors:
-            if t.dtype != head.dtype or not t.is_contiguous():
-                raise RuntimeError("apex_b200: bucket tensors must be contiguous and of one type")
+            if t.dtype != head.dtype or not is_dense(t):
+                raise RuntimeError("apex_b200: bucket tensors must be dense and of one type")
             total += t.numel()
         world = dist.get_world_size()
         if self.flat is None or total != self.total or self.flat.dtype != head.dtype:

@@ -26,7 +26,9 @@ def _bits(t):
 
 
 def _flat(t):
-    return _bits(t).reshape(-1)
+    """1-D numpy view of the tensor's MEMORY (dense tensors only), like the kernels see it."""
+    t = t.detach()
+    return _bits(t.as_strided((t.numel(),), (1,), t.storage_offset()))
 
 
 def _flag_set(flag):

@@ -450,3 +450,36 @@ def test_closure_retries_while_the_gradients_overflow():
     assert out.getvalue().count("OVERFLOW within closure! Skipping step.") == 2
     assert torch.equal(p.data, torch.full((1000,), 0.875, device=dev()).half())
     assert opt.first_closure_call_this_step is True
+
+
+def test_channels_last_conv_model_trains_like_the_reference():
+    """Real autograd gradients of a channels_last fp16 conv net: optimizer.backward / step against the
+    reference composition (apex_ref) driven by the same losses."""
+    def build():
+        torch.manual_seed(3)
+        net = torch.nn.Sequential(torch.nn.Conv2d(3, 16, 3, padding=1), torch.nn.ReLU(),
+                                  torch.nn.Conv2d(16, 8, 1), torch.nn.Flatten(), torch.nn.Linear(8 * 8 * 8, 10))
+        return net.to(dev()).half().to(memory_format=torch.channels_last)
+    a, b = build(), build()
+    assert not a[0].weight.is_contiguous()
+    make = lambda ps: torch.optim.SGD(ps, lr=0.05, momentum=0.9, weight_decay=1e-4)     # noqa: E731
+    kw = dict(dynamic_loss_scale=True, dynamic_loss_args={"init_scale": 2.0**20, "scale_window": 3})
+    opt = FP16_Optimizer(make(list(a.parameters())), verbose=False, **kw)
+    ref = apex_ref.MixedPrecisionStep(list(b.parameters()), make, **kw)
+    g = gen(44)
+    for it in range(10):
+        x = torch.randn(4, 3, 8, 8, generator=g, device=dev()).half().contiguous(memory_format=torch.channels_last)
+        y = torch.randn(4, 10, generator=g, device=dev())
+        a.zero_grad(set_to_none=True)
+        b.zero_grad(set_to_none=True)
+        with contextlib.redirect_stdout(io.StringIO()):
+            opt.backward(torch.nn.functional.mse_loss(a(x).float(), y))
+            opt.step()
+            (torch.nn.functional.mse_loss(b(x).float(), y) * ref.loss_scale).backward()
+            ref.update_master_grads()
+            ref.step()
+        assert opt.overflow == ref.overflow and float(opt.loss_scale) == float(ref.loss_scale), it
+    assert float(opt.loss_scale) < 2.0**20      # the scale did walk down: overflowing iterations were skipped
+    for m, rm, p, q in zip(opt.fp32_from_fp16_groups[0], ref.masters, a.parameters(), b.parameters()):
+        assert m.stride() == p.stride()
+        assert torch.equal(m.data, rm.data) and torch.equal(p.data, q.data)

@@ -580,3 +580,41 @@ def test_two_param_groups_with_their_own_hyperparameters(cpu_backend):
     opt.update_master_grads()
     opt.step()
     assert torch.allclose(extra.data, torch.full((4,), 1.0 - 1.0 / 16))   # lr 1.0, its gradient was unscaled too
+
+
+def test_channels_last_tensors_are_handled_in_place(cpu_backend):
+    """Conv weights (and their gradients) in torch.channels_last are dense but not row-major; the
+    kernels walk memory order, which is legal because gradient, master, state and fp16 copy all
+    share the parameter's strides."""
+    from apex_b200.fp16_utils import FP16_Optimizer
+    from oracle import apex_ref
+    torch.manual_seed(13)
+    init = [(torch.randn(8, 4, 3, 3) * 0.1).half().contiguous(memory_format=torch.channels_last),
+            (torch.randn(16) * 0.1).half(),
+            (torch.randn(6, 8, 1, 1) * 0.1).half().contiguous(memory_format=torch.channels_last)]
+    assert not init[0].is_contiguous()
+    ps = [torch.nn.Parameter(t.clone(memory_format=torch.preserve_format)) for t in init]
+    rs = [torch.nn.Parameter(t.clone(memory_format=torch.preserve_format)) for t in init]
+    make = lambda q: torch.optim.SGD(q, lr=0.1, momentum=0.9, weight_decay=1e-3)     # noqa: E731
+    opt = FP16_Optimizer(make(ps), dynamic_loss_scale=True, dynamic_loss_args={"init_scale": 64.0}, verbose=False)
+    ref = apex_ref.MixedPrecisionStep(rs, make, dynamic_loss_scale=True, dynamic_loss_args={"init_scale": 64.0})
+    assert opt.fp32_from_fp16_groups[0][0].stride() == ps[0].stride()
+    for it in range(4):
+        for p, r in zip(ps, rs):
+            g = (torch.randn(p.shape) * 8).half()
+            if p.dim() == 4:
+                g = g.contiguous(memory_format=torch.channels_last)     # autograd keeps the parameter's layout
+            if it == 1 and p is ps[2]:
+                g[3, 5, 0, 0] = float("inf")
+            p.grad, r.grad = g.clone(memory_format=torch.preserve_format), g.clone(memory_format=torch.preserve_format)
+        opt.update_master_grads()
+        if it == 2:
+            assert torch.equal(opt.fp32_from_fp16_groups[0][0].grad, ps[0].grad.float() * (1. / opt.loss_scale))
+        opt.step()
+        ref.update_master_grads()
+        ref.step()
+        assert opt.overflow == ref.overflow
+    assert "fused_sgd" in cpu_backend.calls
+    for m, rm, p, r in zip(opt.fp32_from_fp16_groups[0], ref.masters, ps, rs):
+        assert torch.equal(m.data, rm.data) and torch.equal(p.data, r.data)
+        assert torch.equal(opt.optimizer.state[m]["momentum_buffer"], ref.optimizer.state[rm]["momentum_buffer"])
