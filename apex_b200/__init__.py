@@ -32,6 +32,7 @@ def install_as_apex():
         "apex.fp16_utils.fused_weight_norm": fused_weight_norm,
         "apex.parallel": parallel,
         "apex.parallel.distributed": distributed,
+        "apex.parallel.LARC": sys.modules[__name__ + ".parallel.LARC"],
         "apex.amp": amp,
         "apex.amp.scaler": scaler,
         "apex.amp.handle": handle,
