@@ -76,14 +76,69 @@ for mb in [int(x) for x in os.environ.get("SIZES_MB", "256,1024").split(",")]:
             assert rc == 0, rc
             h.barrier(channel=1)
         return fn
+    full = os.environ.get("FULL", "0") == "1"
     for variant, label in ((0, "fused T512 U4"), (1, "fused T1024 U4"), (2, "fused T512 U8"), (3, "fused T256 U8"),
                            (4, "fused weak"), (5, "fused no acc::f32"), (6, "fused U1"), (7, "fused U16"),
                            (10, "reduce only"), (11, "bcast only"), (12, "reduce ; bcast U8")):
-        for ctas in (32, 64, 148):
-            if variant in (1, 3, 6, 7, 10, 11) and ctas != 64:
+        if not full and variant not in (0, 10, 11):
+            continue
+        for ctas in (16, 32, 64, 148):
+            if (variant in (1, 3, 6, 7, 10, 11) and ctas != 64) or (not full and variant == 0 and ctas > 32):
                 continue
             buf.fill_(0.001)
             report("ours v%d %s ctas=%d" % (variant, label, ctas), timed(ours(variant, ctas)), nbytes)
+    # reduce and broadcast as separate kernels on two streams, chunked so that bcast(c) overlaps reduce(c+1)
+    tune.symm_tune_launch_range.argtypes = [ctypes.c_int, ctypes.c_uint64, ctypes.c_uint64, ctypes.c_int64,
+                                            ctypes.c_int64, ctypes.c_int, ctypes.c_void_p]
+    sa, sb = torch.cuda.Stream(), torch.cuda.Stream()
+    count = n // 8 // world
+    first = count * rank
+
+    def split(chunks, ctas):
+        def fn():
+            cur = torch.cuda.current_stream()
+            h.barrier(channel=0)
+            start = torch.cuda.Event()
+            start.record()
+            sa.wait_event(start)
+            sb.wait_event(start)
+            per = (count + chunks - 1) // chunks
+            for c in range(chunks):
+                f0 = first + c * per
+                cnt = min(per, count - c * per)
+                if cnt <= 0:
+                    break
+                with torch.cuda.stream(sa):
+                    tune.symm_tune_launch_range(10, mc, mine, f0, cnt, ctas, sa.cuda_stream)
+                    ev = torch.cuda.Event()
+                    ev.record()
+                with torch.cuda.stream(sb):
+                    sb.wait_event(ev)
+                    tune.symm_tune_launch_range(11, mc, mine, f0, cnt, ctas, sb.cuda_stream)
+            cur.wait_stream(sa)
+            cur.wait_stream(sb)
+            h.barrier(channel=1)
+        return fn
+    for chunks in (2, 4, 8):
+        for ctas in (16, 32):
+            buf.fill_(0.001)
+            report("split reduce|bcast chunks=%d ctas=%d" % (chunks, ctas), timed(split(chunks, ctas)), nbytes)
+    # two fused kernels on two streams, each half of the slice
+    def two_fused(ctas):
+        def fn():
+            cur = torch.cuda.current_stream()
+            h.barrier(channel=0)
+            start = torch.cuda.Event()
+            start.record()
+            half = count // 2
+            for st, f0, cnt in ((sa, first, half), (sb, first + half, count - half)):
+                st.wait_event(start)
+                tune.symm_tune_launch_range(0, mc, mine, f0, cnt, ctas, st.cuda_stream)
+                cur.wait_stream(st)
+            h.barrier(channel=1)
+        return fn
+    buf.fill_(0.001)
+    report("two fused halves on two streams ctas=16", timed(two_fused(16)), nbytes)
     # the library entry point, both modes
     for label, mcp, ctas in (("lib multicast", mc, 64), ("lib p2p", 0, 148)):
         def fn():

@@ -93,3 +93,18 @@ extern "C" int symm_tune_launch(int variant, uint64_t mc_ptr, uint64_t my_ptr, i
     }
     return int(cudaPeekAtLastError());
 }
+
+// explicit 16-byte-vector range [first, first+count): for chunked, two-stream overlap experiments
+extern "C" int symm_tune_launch_range(int variant, uint64_t mc_ptr, uint64_t my_ptr, int64_t first, int64_t count,
+                                      int ctas, void* stream) {
+    char* mc = reinterpret_cast<char*>(mc_ptr);
+    char* mine = reinterpret_cast<char*>(my_ptr);
+    cudaStream_t s = static_cast<cudaStream_t>(stream);
+    switch (variant) {
+        case 0: k_fused<512, 4, 0><<<ctas, 512, 0, s>>>(mc, first, count); break;
+        case 10: k_reduce<512, 4><<<ctas, 512, 0, s>>>(mc, mine, first, count); break;
+        case 11: k_bcast<512, 4><<<ctas, 512, 0, s>>>(mc, mine, first, count); break;
+        default: return -1;
+    }
+    return int(cudaPeekAtLastError());
+}
