@@ -420,19 +420,24 @@ class FP16_Optimizer(object):
                     grads.append(param.grad)
         if not grads:
             return
-        flags = []
-        for g in grads:
-            if g.dtype == torch.float32:
-                flags.append(_C.TF_GRAD_F32)
-            elif g.dtype == torch.float16:
-                flags.append(0)
-            else:
-                raise TypeError("apex_b200: unexpected gradient dtype %s" % g.dtype)
         self._ensure_device(grads[0])
-        if self._zero_table is None:
-            self._zero_table = TensorTable(self._device, 1, CHUNK_ZERO)
-        self._zero_table.update([grads], flags)
-        _C.mt_zero(self._zero_table, 0, 2)
+        table = self._zero_table
+        if table is None:
+            table = self._zero_table = TensorTable(self._device, 1, CHUNK_ZERO)
+        if not table.built_from(grads):
+            flags = []
+            for g in grads:
+                if not is_dense(g):
+                    raise RuntimeError("apex_b200: gradients must be dense (contiguous or channels-last)")
+                if g.dtype == torch.float32:
+                    flags.append(_C.TF_GRAD_F32)
+                elif g.dtype == torch.float16:
+                    flags.append(0)
+                else:
+                    raise TypeError("apex_b200: unexpected gradient dtype %s" % g.dtype)
+            table.update([grads], flags)
+            table.remember(grads)
+        _C.mt_zero(table, 0, 2)
 
     # ---- overflow check ----------------------------------------------------------
 
@@ -568,13 +573,20 @@ class FP16_Optimizer(object):
         if self.overflow:
             return -1
         if self._pending is not None and self._clip is None and norm_type in (2, 2.0) \
-                and self.clip_grad_norm is clip_grad_norm:
+                and self.clip_grad_norm is clip_grad_norm and self._groups_intact():
             return self._clip_virtual(max_norm)
         fp32_params = []
         for param_group in self.optimizer.param_groups:
             for param in param_group['params']:
                 fp32_params.append(param)
         return self.clip_grad_norm(fp32_params, max_norm, norm_type)
+
+    def _groups_intact(self):
+        """The inner optimizer's param groups still hold exactly the parameters seen at construction."""
+        groups = self.optimizer.param_groups
+        return len(groups) == len(self.fp16_groups) and all(
+            len(g['params']) == len(h) + len(f)
+            for g, h, f in zip(groups, self.fp16_groups, self.fp32_from_fp32_groups))
 
     def _clip_virtual(self, max_norm):
         inv_scale, apply_scale = self._pending
@@ -732,8 +744,8 @@ class FP16_Optimizer(object):
         inv_scale, apply_scale = (1.0, False) if from_masters else pending
         clip = None if from_masters else self._clip
         plans = []
-        if len(self.optimizer.param_groups) != len(self.fp16_groups):
-            return None           # a group was added after wrapping: the inner optimizer handles it
+        if not self._groups_intact():
+            return None           # groups were edited after wrapping: the inner optimizer handles it
         for gi, group in enumerate(self.optimizer.param_groups):
             plan = self._plan_for(kind, gi, group, from_masters)
             if plan is False:
@@ -822,9 +834,7 @@ class FP16_Optimizer(object):
         # fp32-native parameters are the user's own tensors: unscale in place now.
         if apply_scale:
             groups = self.optimizer.param_groups
-            if len(groups) == len(self.fp16_groups) and all(
-                    len(g['params']) == len(h) + len(f)
-                    for g, h, f in zip(groups, self.fp16_groups, self.fp32_from_fp32_groups)):
+            if self._groups_intact():
                 grads = [p.grad for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
             else:
                 # param_groups were edited after wrapping: the reference unscales the gradient of
