@@ -131,9 +131,20 @@ class _BucketPipeline(object):
         self.scatter_stream = torch.cuda.Stream()
         self.symm_pipe = None          # created when the symmetric-memory path is first used
         self.slots = {}
+        self._spare = []
 
     def reset(self):
+        """The bucket structure changed.  Symmetric-memory slices cannot be given back, so the
+        slots are kept aside and reused by new buckets of the same size and dtype."""
+        self._spare.extend(s for s in self.slots.values() if isinstance(s, symm.SymmSlot))
         self.slots = {}
+
+    def _symm_slot(self, bucket):
+        total = sum(t.numel() for t in bucket)
+        for i, spare in enumerate(self._spare):
+            if spare.total == total and spare.flat is not None and spare.flat.dtype == bucket[0].dtype:
+                return self._spare.pop(i)
+        return symm.SymmSlot()
 
     def submit(self, key, bucket, flag=None):
         """Enqueue the averaging of ``bucket``; returns at once.  Call from inside
@@ -153,7 +164,7 @@ class _BucketPipeline(object):
             slot = self.slots.get(key)
             try:
                 if not isinstance(slot, symm.SymmSlot):
-                    slot = symm.SymmSlot()
+                    slot = self._symm_slot(bucket)
                     slot.bind(bucket)             # allocation + rendezvous: may not be possible on this box
                     self.slots[key] = slot
             except RuntimeError as err:           # every rank fails alike: the rendezvous is collective
@@ -182,15 +193,17 @@ class _BucketPipeline(object):
         stream.wait_stream(self.scatter_stream)
 
 
-def flat_dist_call(tensors, call, extra_args=None):
+def flat_dist_call(tensors, call, extra_args=None, _keep_buffers=True):
     """One flat call per tensor type, types taken in first-seen order.
-    reference: distributed.py:27-38"""
+    reference: distributed.py:27-38.  ``_keep_buffers=False`` (internal) releases the coalesced
+    buffers afterwards: for one-off calls such as the initial broadcast or the flat allreduce of the
+    iteration that learns the bucket structure (one buffer as large as all gradients)."""
     flat_dist_call.warn_on_half = True
     per_type = OrderedDict()
     for t in tensors:
         per_type.setdefault(t.type(), []).append(t)
     for same_type in per_type.values():
-        apply_flat_dist_call(same_type, call, extra_args)
+        apply_flat_dist_call(same_type, call, extra_args, _slot=None if _keep_buffers else _FlatSlot())
 
 
 def extract_tensors(maybe_tensor, tensor_list):
@@ -217,7 +230,7 @@ class Reducer(object):
     def __init__(self, module_or_grads_list):
         if isinstance(module_or_grads_list, Module):
             self.module = module_or_grads_list
-            flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,))
+            flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,), _keep_buffers=False)
         else:
             self.module = None
             self.grads = []
@@ -382,7 +395,7 @@ class DistributedDataParallel(Module):
         self._pipeline = _BucketPipeline(self.reduction_stream)
 
         self.create_hooks()
-        flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,))
+        flat_dist_call([p.data for p in self.module.parameters()], dist.broadcast, (0,), _keep_buffers=False)
 
     # ---- views of the structure under the reference's attribute names ---------------
 
@@ -475,7 +488,8 @@ class DistributedDataParallel(Module):
             self.sync_bucket_structure()
             self.needs_refresh = False
         grads = [p.grad.data for p in self.module.parameters() if p.grad is not None]
-        flat_dist_call(grads, dist.all_reduce)
+        # with delay_allreduce this runs every iteration: keep the buffers then
+        flat_dist_call(grads, dist.all_reduce, _keep_buffers=self.delay_allreduce)
 
     def _finish_backward_overlapped(self):
         """reference ``overlapping_backward_epilogue``: :223-233"""
