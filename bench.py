@@ -256,7 +256,7 @@ def run_reference_arm(args, shapes):
         "e2e": {"value": value, "unit": "params/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line))
+    emit(line)
     return 0
 
 
@@ -303,7 +303,28 @@ def build_buckets(params, bucket_elems):
     return layout.members
 
 
+_json_out = None
+
+
+def protect_stdout():
+    """Keep stdout for the ONE JSON line: anything else that writes to file descriptor 1 (NCCL prints
+    its version banner there when NCCL_DEBUG is set) is sent to stderr instead."""
+    global _json_out
+    if _json_out is None:
+        sys.stdout.flush()
+        _json_out = os.fdopen(os.dup(1), "w")
+        os.dup2(2, 1)
+        sys.stdout = sys.stderr
+
+
+def emit(line):
+    out = _json_out if _json_out is not None else sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    protect_stdout()
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
@@ -536,7 +557,7 @@ def main():
                                  "frac_of_900": algbw * 2 * (world - 1) / world / 900.0,
                                  "includes": "whole bucket path: gather + allreduce + x(1/N) scatter per bucket, the "
                                              "three stages of consecutive buckets overlapped on side streams"}
-        print(json.dumps(line))
+        emit(line)
     if world > 1:
         dist.destroy_process_group()
     return 0
