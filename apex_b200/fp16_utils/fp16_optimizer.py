@@ -341,6 +341,7 @@ class FP16_Optimizer(object):
         # device-side plumbing (created on first use)
         self._device = None
         self._flag = None                # the single overflow word
+        self._flag_src = None            # the word the pending decision lives in (ours, or DDP's)
         self._flag_host = None           # its pinned host mirror
         self._check_table = None         # all gradients, for the overflow scan
         self._unscale_table = None       # fp32-native gradients, unscaled in place
@@ -389,7 +390,7 @@ class FP16_Optimizer(object):
 
     def _live_flag(self):
         """Device word that predicates kernels, or None when no check is pending/needed."""
-        return self._flag if self._overflow_event is not None else None
+        return self._flag_src if self._overflow_event is not None else None
 
     # ---- zero_grad -------------------------------------------------------------
 
@@ -464,6 +465,19 @@ class FP16_Optimizer(object):
             self.overflow = False
             return
         self._ensure_device(grads[0])
+        # Multi-GPU: DistributedDataParallel's scatter pass has already looked at every averaged
+        # value it wrote; if that covers all of our gradients and nothing touched them since, its
+        # flag word IS the answer and no extra pass over the gradients is needed.
+        from ..parallel.distributed import verified_flag
+        ready = verified_flag(grads)
+        if ready is not None and ready.device == self._device:
+            self._flag_src = ready
+            self._flag_host.copy_(ready, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+            self._overflow_event = ev
+            return
+        self._flag_src = self._flag
         table = self._check_table
         if table is None:
             table = self._check_table = TensorTable(self._device, 1, CHUNK_CHECK)

@@ -114,6 +114,40 @@ def apply_flat_dist_call(bucket, call, extra_args=None, _slot=None, _flag=None):
         _C.mt_scale_unflatten(slot.table, flat, 0, 1.0, False, None)
 
 
+class _Verified(object):
+    """What a gradient tensor carries after its bucket went through the scatter-with-check pass:
+    which device word would have been raised had the averaged values held an inf/NaN, in which
+    round, and the tensor's version counter at that moment (any later in-place torch op on the
+    gradient changes the counter and voids the verification)."""
+
+    __slots__ = ("flag", "round_id", "done")
+
+    def __init__(self, flag, round_id):
+        self.flag = flag
+        self.round_id = round_id
+        self.done = False          # set once the round's streams have been joined
+
+
+VERIFIED_ATTR = "_apex_b200_verified"
+
+
+def verified_flag(grads):
+    """If every gradient in ``grads`` was averaged AND checked by one completed pipeline round and
+    has not been touched since, return that round's device flag word; else None.  Used by
+    FP16_Optimizer so that the overflow check of the reference's update_master_grads
+    (fp16_optimizer.py:493-495) costs no extra pass over the gradients on multi-GPU runs."""
+    token = None
+    for g in grads:
+        mark = getattr(g, VERIFIED_ATTR, None)
+        if mark is None:
+            return None
+        t, version = mark
+        if g._version != version or not t.done or (token is not None and t is not token):
+            return None
+        token = t
+    return None if token is None else token.flag
+
+
 class _BucketPipeline(object):
     """Averages buckets with the three stages of consecutive buckets overlapped:
 
@@ -132,6 +166,31 @@ class _BucketPipeline(object):
         self.symm_pipe = None          # created when the symmetric-memory path is first used
         self.slots = {}
         self._spare = []
+        self.check_flag = None         # device word raised by the scatter pass of the current round
+        self._token = None
+        self._round_id = 0
+
+    def begin_round(self):
+        """A new backward starts: gradients verified from now on belong to a fresh round."""
+        self._round_id += 1
+        self._token = None
+
+    def _mark(self, bucket):
+        """Called when a bucket is submitted: clear the round's flag before its first bucket, and
+        tag every gradient of the bucket."""
+        dev = bucket[0].device
+        if self.check_flag is None or self.check_flag.device != dev:
+            self.check_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+        if self._token is None:
+            self._token = _Verified(self.check_flag, self._round_id)
+            _C.flag_clear(self.check_flag)          # on the gather stream, before any scatter of this round
+            self._cleared = torch.cuda.Event()
+            self._cleared.record()
+            self.scatter_stream.wait_event(self._cleared)
+        token = self._token
+        for g in bucket:
+            setattr(g, VERIFIED_ATTR, (token, g._version))
+        return self.check_flag
 
     def reset(self):
         """The bucket structure changed.  Symmetric-memory slices cannot be given back, so the
@@ -146,11 +205,14 @@ class _BucketPipeline(object):
                 return self._spare.pop(i)
         return symm.SymmSlot()
 
-    def submit(self, key, bucket, flag=None):
+    def submit(self, key, bucket, flag=None, verify=False):
         """Enqueue the averaging of ``bucket``; returns at once.  Call from inside
-        ``with torch.cuda.stream(gather_stream)``."""
+        ``with torch.cuda.stream(gather_stream)``.  ``verify=True``: the scatter pass also checks the
+        averaged values and the gradients are tagged so that FP16_Optimizer can skip its own scan."""
         if len(bucket) == 0:
             return
+        if verify and flag is None and bucket[0].dtype in (torch.float16, torch.float32):
+            flag = self._mark(bucket)
         world = dist.get_world_size()
         if len(bucket) == 1 and bucket[0].is_contiguous():
             only = bucket[0]
@@ -186,11 +248,14 @@ class _BucketPipeline(object):
             _C.mt_scale_unflatten(slot.table, flat, 0, world, True, flag)
 
     def join(self, stream):
-        """Make ``stream`` wait for everything submitted so far."""
+        """Make ``stream`` wait for everything submitted so far; the round's verification is then
+        usable by work enqueued on ``stream``."""
         stream.wait_stream(self.gather_stream)
         if self.symm_pipe is not None:
             self.symm_pipe.join(stream)
         stream.wait_stream(self.scatter_stream)
+        if self._token is not None:
+            self._token.done = True
 
 
 def flat_dist_call(tensors, call, extra_args=None, _keep_buffers=True):
@@ -500,14 +565,16 @@ class DistributedDataParallel(Module):
         """``param``'s gradient is final: file it, and reduce whatever became eligible on
         the side stream (reference: :279-315)."""
         bucket_idx, bucket_loc = self._where[id(param)]
-        eligible = self._round.put(bucket_idx, bucket_loc, param.grad.data)
+        # the gradient tensor itself (not a `.data` alias): the scatter pass tags the very object the
+        # optimizer will later find in param.grad
+        eligible = self._round.put(bucket_idx, bucket_loc, param.grad)
         if not eligible:
             return
         # the gradients were produced on the current stream
         self.reduction_stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.reduction_stream):
             for b in eligible:
-                self._pipeline.submit(b, self._round.grads[b])
+                self._pipeline.submit(b, self._round.grads[b], verify=True)
 
     # ---- forward -----------------------------------------------------------------------------
 
@@ -531,6 +598,7 @@ class DistributedDataParallel(Module):
                 self._index_of = {id(p): i for i, p in enumerate(trainable)}
             else:
                 self._round = _BucketRound(self._layout.sizes)
+                self._pipeline.begin_round()
 
             self.active_params = trainable
 

@@ -389,10 +389,11 @@ def main():
         e0 = torch.cuda.Event(enable_timing=True)
         e1 = torch.cuda.Event(enable_timing=True)
         e0.record()
+        pipeline.begin_round()                       # DistributedDataParallel.forward does this
         side.wait_stream(cur)
         with torch.cuda.stream(side):
             for k, b in enumerate(buckets):
-                pipeline.submit(k, b)
+                pipeline.submit(k, b, verify=True)   # as comm_ready_buckets submits them
         pipeline.join(cur)
         e1.record()
         comm_events.append((e0, e1))

@@ -220,6 +220,9 @@ class _Stream(object):
     def wait_stream(self, other):
         pass
 
+    def wait_event(self, event):
+        pass
+
 
 _real_type = torch.Tensor.type
 

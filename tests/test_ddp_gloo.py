@@ -225,3 +225,70 @@ def test_world_size_two(tmp_path):
         assert {"flatten", "scale_unflatten", "scale_flat"} <= set(r["ddp_calls"])
     # rank 0 dictates the structure: identical on both ranks
     assert results[0]["ddp_layout"] == results[1]["ddp_layout"] == (3, [3, 1, 2])
+
+
+def test_scatter_pass_hands_its_overflow_check_to_the_optimizer(gloo_single):
+    """On multi-GPU runs the averaged gradients are inspected by the scatter pass that writes them; the
+    optimizer then needs no scan of its own -- unless something touched the gradients in between."""
+    from apex_b200.fp16_utils import FP16_Optimizer
+    from apex_b200.parallel.distributed import _BucketPipeline, verified_flag
+    from tests import fake_backend as fb
+    calls = gloo_single.calls
+    ps = [torch.nn.Parameter((torch.randn(n) * 0.1).half()) for n in (40, 7, 300)]
+    ps.append(torch.nn.Parameter(torch.randn(12) * 0.1))                     # an fp32 parameter too
+    opt = FP16_Optimizer(torch.optim.SGD(ps, lr=0.1), dynamic_loss_scale=True,
+                         dynamic_loss_args={"init_scale": 4.0}, verbose=False)
+    pipe = _BucketPipeline(fb._Stream())
+
+    def backward_with_ddp(bad=None, grads_seed=0):
+        g = torch.Generator().manual_seed(grads_seed)
+        for i, p in enumerate(ps):
+            p.grad = (torch.randn(p.shape, generator=g) * 4).to(p.dtype)
+            if bad == i:
+                p.grad[3] = float("inf")
+        pipe.begin_round()
+        pipe.submit(0, [p.grad for p in ps[:3]], verify=True)               # the fp16 bucket
+        pipe.submit(1, [ps[3].grad, ps[3].grad.new_zeros(5)], verify=True)   # an fp32 bucket (2 tensors)
+        pipe.join(fb._Stream())
+
+    backward_with_ddp()
+    assert verified_flag([p.grad for p in ps]) is pipe.check_flag
+    n = calls.count("check")
+    opt.update_master_grads()
+    opt.step()
+    assert calls.count("check") == n and opt.overflow is False               # no scan of its own
+    backward_with_ddp(bad=1, grads_seed=1)
+    before = [p.data.clone() for p in ps]
+    opt.update_master_grads()
+    import contextlib, io
+    with contextlib.redirect_stdout(io.StringIO()) as out:
+        opt.step()
+    assert calls.count("check") == n and opt.overflow is True and "OVERFLOW!" in out.getvalue()
+    assert all(torch.equal(a, p.data) for a, p in zip(before, ps)) and opt.loss_scale == 2.0
+    # a gradient edited after the averaging is no longer covered: the optimizer scans again
+    backward_with_ddp(grads_seed=2)
+    ps[0].grad.mul_(1.0)
+    assert verified_flag([p.grad for p in ps]) is None
+    opt.update_master_grads()
+    opt.step()
+    assert calls.count("check") == n + 1 and opt.overflow is False
+    # an inf written after the averaging is caught by that scan
+    backward_with_ddp(grads_seed=3)
+    ps[2].grad[0] = float("nan")
+    opt.update_master_grads()
+    with contextlib.redirect_stdout(io.StringIO()):
+        opt.step()
+    assert opt.overflow is True and calls.count("check") == n + 2
+    # gradients that were never averaged (no DDP) are scanned as before
+    for p in ps:
+        p.grad = torch.zeros_like(p)
+    opt.update_master_grads()
+    assert calls.count("check") == n + 3
+    # a round that has not been joined yet does not count
+    for i, p in enumerate(ps):
+        p.grad = torch.ones_like(p)
+    pipe.begin_round()
+    pipe.submit(0, [p.grad for p in ps[:3]], verify=True)
+    assert verified_flag([p.grad for p in ps[:3]]) is None
+    pipe.join(fb._Stream())
+    assert verified_flag([p.grad for p in ps[:3]]) is pipe.check_flag

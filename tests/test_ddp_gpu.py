@@ -159,6 +159,9 @@ def _worker(rank, world, port, out_dir):
             want /= world
             good &= bool(torch.allclose(p.grad, want, rtol=1e-5, atol=1e-6))
     ok["ddp_real_model"] = bool(good)
+    # the overlapped iterations tagged the gradients: an FP16_Optimizer would not need its own scan
+    from apex_b200.parallel.distributed import verified_flag
+    ok["ddp_grads_verified"] = verified_flag([p.grad for p in net.parameters()]) is ddp._pipeline.check_flag
     ok["ddp_real_model_buckets"] = ddp.num_buckets
     ok["ddp_used_symm"] = any(type(s).__name__ == "SymmSlot" for s in ddp._pipeline.slots.values())
 
@@ -216,7 +219,42 @@ def test_two_ranks_nccl(tmp_path):
         res = torch.load(os.path.join(str(tmp_path), "rank%d.pt" % r), weights_only=False)
         assert res["ddp_real_model_buckets"] >= 2
         for key in ("race", "fp16_average", "fp16_overflow_stays_inf", "ddp_real_model", "ddp_used_symm",
+                    "ddp_grads_verified",
                     "symm_auto", "symm_p2p", "symm_auto_overflow", "symm_p2p_overflow"):
             assert res[key] is True, (key, res)
         print("multicast used:", res["symm_auto_multicast"], "| bits equal to reference composition:",
               res["fp16_same_bits_as_reference_composition"], "| symm default:", res["symm_default_on"])
+
+
+def test_ddp_plus_fp16_optimizer_skips_its_own_scan_single_rank(nccl_single):
+    """DDP (overlapped iterations) + FP16_Optimizer with dynamic scaling: from the second iteration on
+    the step consists of the fused update only -- the check was done by DDP's scatter pass -- and an
+    overflow produced by backward is still caught."""
+    from apex_b200 import _C
+    from apex_b200.parallel import DistributedDataParallel as DDP
+    from apex_b200.fp16_utils import FP16_Optimizer
+    torch.manual_seed(0)
+    model = torch.nn.Sequential(torch.nn.Linear(64, 128), torch.nn.ReLU(), torch.nn.Linear(128, 16)).cuda().half()
+    ddp = DDP(model, message_size=2000)
+    opt = FP16_Optimizer(torch.optim.SGD(model.parameters(), lr=0.01, momentum=0.9), dynamic_loss_scale=True,
+                         dynamic_loss_args={"init_scale": 2.0**8}, verbose=False)
+    x = torch.randn(32, 64, device="cuda").half()
+    y = torch.randn(32, 16, device="cuda")
+    real_check = _C.mt_check_overflow
+    scans = []
+    _C.mt_check_overflow = lambda *a, **k: (scans.append(1), real_check(*a, **k))[1]
+    try:
+        for it in range(6):
+            opt.zero_grad()
+            scale_up = 1e6 if it == 4 else 1.0               # iteration 4 overflows in backward
+            loss = torch.nn.functional.mse_loss(ddp(x).float() * scale_up, y)
+            import contextlib, io
+            with contextlib.redirect_stdout(io.StringIO()):
+                opt.backward(loss)
+                opt.step()
+            assert opt.overflow == (it == 4), it
+    finally:
+        _C.mt_check_overflow = real_check
+    # zero_grad() zeroes the gradients in place through our own kernel (no version change), autograd then
+    # accumulates into them (version change) BEFORE DDP averages and tags them -> still covered.
+    assert len(scans) <= 2, scans        # the learning iteration (and at most one more) scanned; the rest did not
