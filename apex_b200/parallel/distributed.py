@@ -120,12 +120,13 @@ class _Verified(object):
     round, and the tensor's version counter at that moment (any later in-place torch op on the
     gradient changes the counter and voids the verification)."""
 
-    __slots__ = ("flag", "round_id", "done")
+    __slots__ = ("flag", "round_id", "done", "count")
 
     def __init__(self, flag, round_id):
         self.flag = flag
         self.round_id = round_id
         self.done = False          # set once the round's streams have been joined
+        self.count = 0             # gradient tensors checked into this round's flag
 
 
 VERIFIED_ATTR = "_apex_b200_verified"
@@ -145,7 +146,11 @@ def verified_flag(grads):
         if g._version != version or not t.done or (token is not None and t is not token):
             return None
         token = t
-    return None if token is None else token.flag
+    # the word answers "any inf/NaN among ALL gradients of the round": only an optimizer that owns
+    # exactly those gradients may take it as its own answer (the reference checks its own only)
+    if token is None or token.count != len(grads):
+        return None
+    return token.flag
 
 
 class _BucketPipeline(object):
@@ -190,6 +195,7 @@ class _BucketPipeline(object):
         token = self._token
         for g in bucket:
             setattr(g, VERIFIED_ATTR, (token, g._version))
+        token.count += len(bucket)
         return self.check_flag
 
     def reset(self):

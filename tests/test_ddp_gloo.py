@@ -248,7 +248,7 @@ def test_scatter_pass_hands_its_overflow_check_to_the_optimizer(gloo_single):
                 p.grad[3] = float("inf")
         pipe.begin_round()
         pipe.submit(0, [p.grad for p in ps[:3]], verify=True)               # the fp16 bucket
-        pipe.submit(1, [ps[3].grad, ps[3].grad.new_zeros(5)], verify=True)   # an fp32 bucket (2 tensors)
+        pipe.submit(1, [ps[3].grad], verify=True)                            # the fp32 bucket
         pipe.join(fb._Stream())
 
     backward_with_ddp()
@@ -284,6 +284,9 @@ def test_scatter_pass_hands_its_overflow_check_to_the_optimizer(gloo_single):
         p.grad = torch.zeros_like(p)
     opt.update_master_grads()
     assert calls.count("check") == n + 3
+    # an optimizer that owns only part of the round's gradients must not adopt the round's answer
+    backward_with_ddp(grads_seed=4)
+    assert verified_flag([p.grad for p in ps[:3]]) is None and verified_flag([p.grad for p in ps]) is not None
     # a round that has not been joined yet does not count
     for i, p in enumerate(ps):
         p.grad = torch.ones_like(p)
