@@ -56,6 +56,9 @@ class _OverflowProbe(object):
         return int(self.launch(grads).item()) != 0
 
 
+_shared_probes = {}     # device -> probe used by the class-level DynamicLossScaler._has_inf_or_nan
+
+
 class LossScaler:
     """Fixed loss scale (reference: loss_scaler.py:10-45).  Never reports overflow."""
 
@@ -119,7 +122,10 @@ class DynamicLossScaler:
 
     def _has_inf_or_nan(x):
         """Single tensor form (loss_scaler.py:92-110); no ``self``, as in the reference."""
-        return _OverflowProbe().any_bad([x])
+        probe = _shared_probes.get(x.device)
+        if probe is None:
+            probe = _shared_probes[x.device] = _OverflowProbe()
+        return probe.any_bad([x])
 
     def update_scale(self, overflow):
         if overflow:

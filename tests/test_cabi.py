@@ -60,13 +60,15 @@ def test_version_and_error_strings():
 
 def _pack(numels, n_lists, ptrs, flags, chunk):
     n = len(numels)
-    arr = np.asarray(numels, np.int64)
-    nbytes = _C.table_bytes(n, n_lists, _C.count_chunks(n, arr.ctypes.data if n else None, chunk))
+    # keep the arrays alive for the duration of the calls (ctypes.data of a temporary dangles)
+    a_numel = np.asarray(numels, np.int64)
+    a_ptrs = np.asarray(ptrs, np.uint64)
+    a_flags = None if flags is None else np.asarray(flags, np.int32)
+    nbytes = _C.table_bytes(n, n_lists, _C.count_chunks(n, a_numel.ctypes.data if n else None, chunk))
     buf = np.zeros(nbytes, np.uint8)
     st = _C.table_pack(buf.ctypes.data, nbytes, n, n_lists,
-                       np.asarray(numels, np.int64).ctypes.data if n else None,
-                       np.asarray(ptrs, np.uint64).ctypes.data if n else None,
-                       None if flags is None else np.asarray(flags, np.int32).ctypes.data, chunk)
+                       a_numel.ctypes.data if n else None, a_ptrs.ctypes.data if n else None,
+                       None if a_flags is None else a_flags.ctypes.data, chunk)
     return st, buf
 
 
@@ -150,3 +152,34 @@ def test_product_fails_loudly_without_the_library(tmp_path):
              "    print('IMPORTERROR', 'no python or CPU' in str(e))\n" % ROOT)
     out = subprocess.check_output(["python", "-c", probe]).decode()
     assert "IMPORTERROR True" in out
+
+
+def test_table_pack_properties_on_random_tensor_lists():
+    """For any list of sizes: chunks tile every tensor exactly, in order, and never straddle two tensors."""
+    from hypothesis import given, settings, strategies as st
+
+    @settings(max_examples=60, deadline=None)
+    @given(st.lists(st.integers(min_value=0, max_value=300000), min_size=0, max_size=40),
+           st.sampled_from([2048, 4096, 16384, 65536]), st.integers(min_value=1, max_value=5))
+    def check(numels, chunk, n_lists):
+        n = len(numels)
+        ptrs = [32 * (7 + i + l * 1000) for l in range(n_lists) for i in range(n)]
+        st_, buf = _pack(numels, n_lists, ptrs, None, chunk)
+        off = 16 + 8 * n + 8 * (n + 1) + 8 * n * n_lists + 4 * n
+        off = (off + 7) & ~7
+        t_chunk = np.frombuffer(buf, np.int32, n + 1, off)
+        off = (off + 4 * (n + 1) + 7) & ~7
+        owner = np.frombuffer(buf, np.int32, st_.total_chunks, off)
+        want_chunks = [-(-x // chunk) for x in numels]
+        assert st_.total_chunks == sum(want_chunks)
+        assert t_chunk.tolist() == [sum(want_chunks[:i]) for i in range(n + 1)]
+        assert owner.tolist() == [i for i, c in enumerate(want_chunks) for _ in range(c)]
+        # every chunk lies inside its tensor and the chunks of a tensor cover it exactly once
+        covered = [0] * n
+        for c, t in enumerate(owner.tolist()):
+            start = (c - t_chunk[t]) * chunk
+            assert 0 <= start < numels[t]
+            covered[t] += min(chunk, numels[t] - start)
+        assert covered == list(numels)
+        assert len(buf) == _C.table_bytes(n, n_lists, st_.total_chunks)
+    check()
