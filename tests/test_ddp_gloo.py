@@ -295,3 +295,44 @@ def test_scatter_pass_hands_its_overflow_check_to_the_optimizer(gloo_single):
     assert verified_flag([p.grad for p in ps[:3]]) is None
     pipe.join(fb._Stream())
     assert verified_flag([p.grad for p in ps[:3]]) is pipe.check_flag
+
+
+def test_bucket_bookkeeping_against_the_oracle_on_random_cases():
+    """_BucketLayout / _BucketRound (host logic, no process group needed) against the restated
+    reference algorithms (oracle/apex_ref.py: distributed.py:248-261, :176-180, :279-315)."""
+    from hypothesis import given, settings, strategies as st
+    from apex_b200.parallel.distributed import _BucketLayout, _BucketRound, _DTYPE_CLASS
+    from oracle import apex_ref
+    dts = [torch.float16, torch.float32, torch.float64]
+
+    @settings(max_examples=150, deadline=None)
+    @given(st.lists(st.tuples(st.integers(0, 2), st.integers(1, 5000)), min_size=1, max_size=30),
+           st.integers(1, 12000), st.randoms(use_true_random=False))
+    def check(spec, message_size, rnd):
+        n = len(spec)
+        dtypes = [dts[c] for c, _ in spec]
+        numels = [k for _, k in spec]
+        arrival = list(range(n))
+        rnd.shuffle(arrival)
+        layout = _BucketLayout(message_size)
+        for i in arrival:
+            layout.arrive(_DTYPE_CLASS[dtypes[i]], i, numels[i])
+        layout.close()
+        buckets, where = apex_ref.bucket_layout(arrival, numels, dtypes, message_size)
+        assert layout.members == buckets
+        assert layout.positions() == where
+        # the vector that is broadcast decodes to the same structure
+        copy = _BucketLayout(message_size)
+        copy.decode(layout.encode())
+        assert copy.members == buckets and copy.sizes == [len(b) for b in buckets]
+        # a later backward in ANOTHER arrival order: issue order must still be 0, 1, 2, ...
+        order = list(range(n))
+        rnd.shuffle(order)
+        rounds = _BucketRound(layout.sizes)
+        issued = []
+        for i in order:
+            b, loc = where[i]
+            issued += rounds.put(b, loc, object())
+        assert issued == apex_ref.dispatch_order([where[i][0] for i in order], layout.sizes) == list(range(len(buckets)))
+        rounds.verify_complete()
+    check()
