@@ -158,6 +158,8 @@ def cpu_reference_run(shapes, steps, warmup, budget_s, seed=1234, kind="adam"):
     calls torch.optim.Adam exactly where apex/fp16_utils/fp16_optimizer.py:380 does) on CPU
     tensors, on a bounded sample of the workload.  Returns (params_per_s, info)."""
     from oracle import apex_ref
+    # all host cores (torchrun exports OMP_NUM_THREADS=1 to every rank; the other ranks idle or have exited)
+    torch.set_num_threads(max(torch.get_num_threads(), os.cpu_count() or 1))
     # bounded sample: leading tensors of the workload up to ~40M elements (embedding excluded if too big)
     sample, total = [], 0
     for s in (shapes[1:] if numel(shapes[0]) > 40_000_000 else shapes):
