@@ -346,6 +346,19 @@ def main():
     kind = args.optimizer
     n_params = sum(numel(s) for s in shapes)
 
+    if args.gpus > 1 and "WORLD_SIZE" not in os.environ:
+        # asked for N GPUs without a launcher: start one rank per GPU ourselves (the driver uses
+        # `python -m torch.distributed.run ... bench.py --gpus N`, which lands in the code below)
+        import socket
+        sock = socket.socket()
+        sock.bind(("127.0.0.1", 0))
+        port = sock.getsockname()[1]
+        sock.close()
+        os.dup2(_json_out.fileno(), 1)            # give the real stdout back to the child ranks
+        cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(args.gpus),
+               "--master-addr", "127.0.0.1", "--master-port", str(port), os.path.abspath(__file__)] + sys.argv[1:]
+        os.execv(sys.executable, cmd)
+
     if args.impl == "reference":
         return run_reference_arm(args, shapes)
 
