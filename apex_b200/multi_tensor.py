@@ -54,22 +54,30 @@ class TensorTable(object):
         self.flags = None
         self.rebuilds = 0
         self._refs = None      # weak references to the tensors the table was built from
+        self._ids = None
+        self._alive = False
+        self._generation = None
 
     # Fast path for callers that run every training step: "are these still the very same tensor
-    # objects the table was built from?" costs a few tens of microseconds for hundreds of tensors,
-    # whereas update() fetches every address again.  Weak references: the table must not keep
-    # gradients alive that the user has dropped (zero_grad(set_to_none=True)).
+    # objects the table was built from?"  The table remembers their id()s; a weak reference per tensor
+    # (the table must not keep gradients alive that the user has dropped) carries a callback that
+    # voids the table the moment one of them dies -- an id can only be reused after that -- so the
+    # per-step test is one C-speed pass over the ids: microseconds for hundreds of tensors, where
+    # update() fetches every address again.
     def built_from(self, objs):
-        refs = self._refs
-        if refs is None or len(refs) != len(objs) or self._key is None:
-            return False
-        for r, o in zip(refs, objs):
-            if r() is not o:
-                return False
-        return True
+        return self._alive and self._key is not None and self._ids == list(map(id, objs))
 
     def remember(self, objs):
-        self._refs = [weakref.ref(o) for o in objs]
+        self._ids = list(map(id, objs))
+        self._alive = True
+        token = self._generation = object()
+        me = weakref.ref(self)
+
+        def died(_ref, token=token, me=me):
+            table = me()
+            if table is not None and table._generation is token:
+                table._alive = False
+        self._refs = [weakref.ref(o, died) for o in objs]
 
     def update(self, lists, flags=None):
         """Point the table at ``lists`` (n_lists sequences of equal length).
@@ -122,6 +130,8 @@ class TensorTable(object):
     def invalidate(self):
         self._key = None
         self._refs = None
+        self._ids = None
+        self._alive = False
 
 
 def is_dense(t):

@@ -183,3 +183,28 @@ def test_table_pack_properties_on_random_tensor_lists():
         assert covered == list(numels)
         assert len(buf) == _C.table_bytes(n, n_lists, st_.total_chunks)
     check()
+
+
+def test_table_identity_fast_path_is_voided_when_a_tensor_dies():
+    """TensorTable.built_from: same objects -> True; a different object, or a remembered tensor that has
+    been freed since (its id may be reused), -> False."""
+    import gc
+    from apex_b200.multi_tensor import TensorTable
+    a, b, c = torch.zeros(8), torch.zeros(8), torch.zeros(8)
+    t = TensorTable("cpu", 1, 2048)
+    t.update([[a, b]])
+    t.remember([a, b])
+    assert t.built_from([a, b]) and not t.built_from([a, c]) and not t.built_from([a]) and not t.built_from([b, a])
+    assert t.update([[a, b]]) is False                    # same addresses: no rebuild
+    del b
+    gc.collect()
+    assert t._alive is False and not t.built_from([a, c])
+    # a table rebuilt afterwards is not affected by the death of tensors of its previous generation
+    d = torch.zeros(8)
+    t.update([[a, d]])
+    t.remember([a, d])
+    del c
+    gc.collect()
+    assert t.built_from([a, d])
+    t.invalidate()
+    assert not t.built_from([a, d])
