@@ -363,6 +363,70 @@ def golden_checkpoint(apex):
                 "final_iter": opt.loss_scaler.cur_iter}, os.path.join(HERE, "reference_checkpoint_after.pt"))
 
 
+def golden_larc(apex, out, arrays):
+    """apex.parallel.LARC (apex/parallel/LARC.py) around SGD, clip and scale modes, a zero-norm
+    parameter and a parameter without gradient."""
+    from importlib import import_module
+    LARC = import_module("apex.parallel.LARC").LARC
+    for clip in (True, False):
+        name = "larc_clip" if clip else "larc_scale"
+        gen = torch.Generator().manual_seed(9)
+        shapes = [(40, 7), (13,), (5, 5, 3), (1,)]
+        init = [torch.randn(s, generator=gen) * 0.3 for s in shapes]
+        init[3].zero_()
+        ps = [torch.nn.Parameter(t.clone()) for t in init]
+        opt = LARC(torch.optim.SGD(ps, lr=0.1, momentum=0.9, weight_decay=5e-4), trust_coefficient=0.02, clip=clip)
+        for i, t in enumerate(init):
+            arrays["%s/init/%d" % (name, i)] = f16(t)
+        for it in range(4):
+            for i, p in enumerate(ps):
+                g = torch.randn(p.shape, generator=gen) * (10.0 if it % 2 else 0.01)
+                arrays["%s/grad/%d/%d" % (name, it, i)] = f16(g)
+                p.grad = g.clone()
+            if it == 2:
+                ps[1].grad = None
+            opt.step()
+        for i, p in enumerate(ps):
+            arrays["%s/final/%d" % (name, i)] = f16(p.data)
+    out["larc"] = {"lr": 0.1, "momentum": 0.9, "weight_decay": 5e-4, "trust_coefficient": 0.02, "iters": 4,
+                   "no_grad": {"iteration": 2, "param": 1}}
+
+
+def golden_amp_handle(apex, out):
+    """AmpHandle.scale_loss / OptimWrapper (apex/amp/handle.py:32-63, opt.py:19-82) driven directly;
+    amp.init()'s function patching is not involved (and cannot run on this torch)."""
+    from importlib import import_module
+    AmpHandle = import_module("apex.amp.handle").AmpHandle
+    log = []
+    w = torch.nn.Parameter(torch.tensor([1.0, 2.0, -1.0]))
+    opt = torch.optim.SGD([w], lr=0.5)
+    handle = AmpHandle()
+    coeffs = [[1.0, 3.0, 0.5], [float("inf"), 1.0, 1.0], [2.0, -1.0, 0.25], [float("nan"), 0.0, 0.0], [1.0, 1.0, 1.0]]
+    for c in coeffs:
+        opt.zero_grad()
+        loss = (w * torch.tensor(c)).sum()
+        with handle.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+        log.append({"w": w.data.tolist(), "scale": handle._default_scaler.loss_scale()})
+    out["amp_handle"] = {"coeffs": [[repr(x) for x in c] for c in coeffs], "log": log}
+    # two losses per iteration through the optimizer wrapper; the second loss overflows in iteration 1
+    w2 = torch.nn.Parameter(torch.tensor([1.0, 1.0]))
+    wrapped = AmpHandle().wrap_optimizer(torch.optim.SGD([w2], lr=0.25), num_loss=2)
+    log2 = []
+    for it in range(3):
+        wrapped.zero_grad()
+        with wrapped.scale_loss((w2 * 2).sum()) as s0:
+            s0.backward()
+        second = torch.tensor([float("inf"), 1.0]) if it == 1 else torch.tensor([3.0, -1.0])
+        with wrapped.scale_loss((w2 * second).sum()) as s1:
+            s1.backward()
+        wrapped.step()
+        log2.append({"w": w2.data.tolist(), "grad": [repr(x) for x in w2.grad.tolist()],
+                     "scales": [sc.loss_scale() for sc in wrapped._loss_scaler]})
+    out["amp_optim_wrapper"] = {"log": log2}
+
+
 def main():
     apex = load_reference()
     golden_checkpoint(apex)
@@ -373,6 +437,8 @@ def main():
     golden_fp16_optimizer(apex, out, arrays)
     golden_fp16util(apex, out, arrays)
     golden_ddp_layout(apex, out)
+    golden_larc(apex, out, arrays)
+    golden_amp_handle(apex, out)
     with open(os.path.join(HERE, "reference_golden.json"), "w") as f:
         json.dump(out, f, indent=1, sort_keys=True)
     np.savez_compressed(os.path.join(HERE, "reference_golden.npz"), **arrays)

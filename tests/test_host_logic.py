@@ -618,3 +618,70 @@ def test_channels_last_tensors_are_handled_in_place(cpu_backend):
     for m, rm, p, r in zip(opt.fp32_from_fp16_groups[0], ref.masters, ps, rs):
         assert torch.equal(m.data, rm.data) and torch.equal(p.data, r.data)
         assert torch.equal(opt.optimizer.state[m]["momentum_buffer"], ref.optimizer.state[rm]["momentum_buffer"])
+
+
+def test_larc_against_golden_runs_of_the_reference(golden_json, golden_arrays, cpu_backend):
+    from apex_b200.parallel import LARC
+    meta = golden_json["larc"]
+    for name, clip in (("larc_clip", True), ("larc_scale", False)):
+        ps = [torch.nn.Parameter(tensor_from(golden_arrays["%s/init/%d" % (name, i)])) for i in range(4)]
+        opt = LARC(torch.optim.SGD(ps, lr=meta["lr"], momentum=meta["momentum"], weight_decay=meta["weight_decay"]),
+                   trust_coefficient=meta["trust_coefficient"], clip=clip)
+        for it in range(meta["iters"]):
+            for i, p in enumerate(ps):
+                p.grad = tensor_from(golden_arrays["%s/grad/%d/%d" % (name, it, i)])
+            if it == meta["no_grad"]["iteration"]:
+                ps[meta["no_grad"]["param"]].grad = None
+            opt.step()
+        for i, p in enumerate(ps):
+            want = golden_arrays["%s/final/%d" % (name, i)]
+            # norms are reduced in another order than torch.norm: a few fp32 ulps on the rate
+            assert np.allclose(p.data.numpy(), want, rtol=3e-6, atol=1e-9), (name, i)
+
+
+def test_oracle_larc_restatement_is_pinned_too(golden_json, golden_arrays):
+    from oracle import apex_ref
+    meta = golden_json["larc"]
+    for name, clip in (("larc_clip", True), ("larc_scale", False)):
+        ps = [torch.nn.Parameter(tensor_from(golden_arrays["%s/init/%d" % (name, i)])) for i in range(4)]
+        inner = torch.optim.SGD(ps, lr=meta["lr"], momentum=meta["momentum"], weight_decay=meta["weight_decay"])
+        for it in range(meta["iters"]):
+            for i, p in enumerate(ps):
+                p.grad = tensor_from(golden_arrays["%s/grad/%d/%d" % (name, it, i)])
+            if it == meta["no_grad"]["iteration"]:
+                ps[meta["no_grad"]["param"]].grad = None
+            apex_ref.larc_rescale(ps, meta["lr"], meta["weight_decay"], meta["trust_coefficient"], clip)
+            inner.param_groups[0]["weight_decay"] = 0
+            inner.step()
+            inner.param_groups[0]["weight_decay"] = meta["weight_decay"]
+        for i, p in enumerate(ps):
+            assert np.array_equal(p.data.numpy(), golden_arrays["%s/final/%d" % (name, i)]), (name, i)
+
+
+def test_amp_handle_and_wrapper_against_golden_runs_of_the_reference(golden_json, cpu_backend):
+    from apex_b200.amp import AmpHandle
+    g = golden_json["amp_handle"]
+    w = torch.nn.Parameter(torch.tensor([1.0, 2.0, -1.0]))
+    opt = torch.optim.SGD([w], lr=0.5)
+    handle = AmpHandle()
+    for c, row in zip(g["coeffs"], g["log"]):
+        opt.zero_grad()
+        loss = (w * torch.tensor([float(x) for x in c])).sum()
+        with handle.scale_loss(loss, opt) as scaled:
+            scaled.backward()
+        opt.step()
+        assert w.data.tolist() == row["w"] and handle._default_scaler.loss_scale() == row["scale"]
+    g2 = golden_json["amp_optim_wrapper"]
+    w2 = torch.nn.Parameter(torch.tensor([1.0, 1.0]))
+    wrapped = AmpHandle().wrap_optimizer(torch.optim.SGD([w2], lr=0.25), num_loss=2)
+    for it, row in enumerate(g2["log"]):
+        wrapped.zero_grad()
+        with wrapped.scale_loss((w2 * 2).sum()) as s0:
+            s0.backward()
+        second = torch.tensor([float("inf"), 1.0]) if it == 1 else torch.tensor([3.0, -1.0])
+        with wrapped.scale_loss((w2 * second).sum()) as s1:
+            s1.backward()
+        wrapped.step()
+        assert w2.data.tolist() == row["w"]
+        assert [repr(x) for x in w2.grad.tolist()] == row["grad"]      # incl. the un-unscaled gradient of the bad loss
+        assert [sc.loss_scale() for sc in wrapped._loss_scaler] == row["scales"]
