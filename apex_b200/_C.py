@@ -114,6 +114,26 @@ def _check(code, what):
         raise RuntimeError("%s failed: %s (code %d)" % (what, error_string(code), code))
 
 
+# APEX_B200_NVTX=1: every kernel wrapper below is bracketed by an NVTX range named after the entry
+# point, so that a timeline (nsys) or `ncu --nvtx-include` can attribute launches to API calls.
+# The reference has no tracing hooks at all.
+if os.environ.get("APEX_B200_NVTX", "0") == "1":
+    import functools
+
+    def _traced(fn):
+        @functools.wraps(fn)
+        def wrapper(*args, **kwargs):
+            torch.cuda.nvtx.range_push("apex_b200." + fn.__name__)
+            try:
+                return fn(*args, **kwargs)
+            finally:
+                torch.cuda.nvtx.range_pop()
+        return wrapper
+else:
+    def _traced(fn):
+        return fn
+
+
 def version():
     return lib.apex_b200_version()
 
@@ -160,18 +180,21 @@ def _count(table):
         launches += 1
 
 
+@_traced
 def mt_check_overflow(table, grad_list, flag, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_check_overflow(table.ref, grad_list, _ptr(flag),
                                            current_stream() if stream is None else stream), "mt_check_overflow")
 
 
+@_traced
 def mt_unscale(table, grad_list, inv_scale, flag, mode, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_unscale(table.ref, grad_list, float(inv_scale), _ptr(flag), mode,
                                     current_stream() if stream is None else stream), "mt_unscale")
 
 
+@_traced
 def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, clip=None, stream=None):
     """clip: None or (device norm tensor, max_norm)."""
     _count(table)
@@ -182,24 +205,28 @@ def mt_grads_to_master(table, src_list, dst_list, inv_scale, apply_scale, flag, 
            "mt_grads_to_master")
 
 
+@_traced
 def mt_master_to_model(table, src_list, dst_list, flag, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_master_to_model(table.ref, src_list, dst_list, _ptr(flag),
                                             current_stream() if stream is None else stream), "mt_master_to_model")
 
 
+@_traced
 def mt_copy(table, src_list, dst_list, elem_size, flag, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_copy(table.ref, src_list, dst_list, elem_size, _ptr(flag),
                                  current_stream() if stream is None else stream), "mt_copy")
 
 
+@_traced
 def mt_zero(table, lst, elem_size, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_zero(table.ref, lst, elem_size, current_stream() if stream is None else stream),
            "mt_zero")
 
 
+@_traced
 def mt_fused_sgd(table, lr, momentum, dampening, weight_decay, nesterov, inv_scale, apply_scale, flag,
                  clip=None, stream=None):
     _count(table)
@@ -210,6 +237,7 @@ def mt_fused_sgd(table, lr, momentum, dampening, weight_decay, nesterov, inv_sca
                                       current_stream() if stream is None else stream), "mt_fused_sgd")
 
 
+@_traced
 def mt_fused_adam(table, lr, beta1, beta2, eps, weight_decay, step_size, bias_correction2_sqrt,
                   decoupled_weight_decay, inv_scale, apply_scale, flag, clip=None, stream=None):
     _count(table)
@@ -220,12 +248,14 @@ def mt_fused_adam(table, lr, beta1, beta2, eps, weight_decay, step_size, bias_co
                                        current_stream() if stream is None else stream), "mt_fused_adam")
 
 
+@_traced
 def mt_flatten(table, src_list, flat, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_flatten(table.ref, src_list, _ptr(flat), flat.element_size(),
                                     current_stream() if stream is None else stream), "mt_flatten")
 
 
+@_traced
 def mt_scale_unflatten(table, flat, dst_list, divisor, apply_mul, flag, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_scale_unflatten(table.ref, _ptr(flat), dst_list, DTYPE_CODE[flat.dtype],
@@ -233,6 +263,7 @@ def mt_scale_unflatten(table, flat, dst_list, divisor, apply_mul, flag, stream=N
                                             current_stream() if stream is None else stream), "mt_scale_unflatten")
 
 
+@_traced
 def scale_flat(flat, divisor, flag, stream=None):
     global launches
     if flat.numel() > 0:
@@ -241,6 +272,7 @@ def scale_flat(flat, divisor, flag, stream=None):
                                     current_stream() if stream is None else stream), "scale_flat")
 
 
+@_traced
 def symm_allreduce(peer_ptrs, multicast_ptr, rank, world, numel, dtype, ctas=0, stream=None):
     """In-place SUM of a symmetric-memory buffer over `world` GPUs (this rank's half of the work)."""
     global launches
@@ -250,6 +282,7 @@ def symm_allreduce(peer_ptrs, multicast_ptr, rank, world, numel, dtype, ctas=0, 
                                         current_stream() if stream is None else stream), "symm_allreduce")
 
 
+@_traced
 def mt_l2norm(table, grad_list, inv_scale, apply_scale, partials, norm_out, stream=None):
     global launches
     launches += 2 if table.struct.total_chunks > 0 else 1
@@ -261,6 +294,7 @@ def mt_l2norm(table, grad_list, inv_scale, apply_scale, partials, norm_out, stre
 NOALLOC_MAX_CHUNKS = 65536
 
 
+@_traced
 def mt_l2norm_noalloc(table, grad_list, inv_scale, apply_scale, norm_out, stream=None):
     """apex_b200_mt_l2norm for callers that cannot allocate scratch (memory pool exhausted, or a
     collective in flight that a cudaMalloc would stall): the partial sums use a fixed 256 KiB array
@@ -273,12 +307,14 @@ def mt_l2norm_noalloc(table, grad_list, inv_scale, apply_scale, norm_out, stream
            "mt_l2norm_noalloc")
 
 
+@_traced
 def mt_clip_by_norm(table, grad_list, norm, max_norm, flag, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_clip_by_norm(table.ref, grad_list, _ptr(norm), float(max_norm), _ptr(flag),
                                          current_stream() if stream is None else stream), "mt_clip_by_norm")
 
 
+@_traced
 def mt_larc(table, grad_list, param_list, trust_coefficient, eps, weight_decay, lr, clip, scratch, norms=None,
             stream=None):
     global launches
