@@ -52,6 +52,18 @@ class AdamArgs(ctypes.Structure):
                 ("inv_scale", ctypes.c_double), ("clip_norm", ctypes.c_void_p), ("clip_max_norm", ctypes.c_double)]
 
 
+SYMM_MAX_WORLD = 16
+SYMM_MAX_CTAS = 256
+SYMM_CHANNELS = 2
+SYMM_SIGNAL_BYTES = SYMM_CHANNELS * SYMM_MAX_CTAS * SYMM_MAX_WORLD * 4
+
+
+class SymmDomain(ctypes.Structure):
+    _fields_ = [("rank", ctypes.c_int32), ("world", ctypes.c_int32),
+                ("peer_base", ctypes.c_uint64 * SYMM_MAX_WORLD), ("multicast_base", ctypes.c_uint64),
+                ("signal_offset", ctypes.c_uint64), ("timeout_ns", ctypes.c_uint64)]
+
+
 _vp = ctypes.c_void_p
 _i = ctypes.c_int
 _d = ctypes.c_double
@@ -67,6 +79,7 @@ SIGNATURES = {
     "apex_b200_mt_table_pack": (_i, [_vp, ctypes.c_size_t, _i, _i, _vp, _vp, _vp, _i, _tp]),
     "apex_b200_flag_clear": (_i, [_vp, _vp]),
     "apex_b200_mt_check_overflow": (_i, [_tp, _i, _vp, _vp]),
+    "apex_b200_mt_check_overflow_publish": (_i, [_tp, _i, _vp, _vp, _vp, _vp, _vp]),
     "apex_b200_mt_unscale": (_i, [_tp, _i, _d, _vp, _i, _vp]),
     "apex_b200_mt_grads_to_master": (_i, [_tp, _i, _i, _d, _i, _vp, _vp, _d, _vp]),
     "apex_b200_mt_master_to_model": (_i, [_tp, _i, _i, _vp, _vp]),
@@ -77,7 +90,8 @@ SIGNATURES = {
     "apex_b200_mt_flatten": (_i, [_tp, _i, _vp, _i, _vp]),
     "apex_b200_mt_scale_unflatten": (_i, [_tp, _vp, _i, _i, _d, _i, _vp, _vp]),
     "apex_b200_scale_flat": (_i, [_vp, ctypes.c_int64, _i, _d, _vp, _vp]),
-    "apex_b200_symm_allreduce": (_i, [_vp, ctypes.c_uint64, _i, _i, ctypes.c_int64, _i, _i, _vp]),
+    "apex_b200_symm_allreduce": (_i, [ctypes.POINTER(SymmDomain), ctypes.c_uint64, ctypes.c_int64, _i, _d, _i,
+                                      ctypes.c_int64, _i, ctypes.c_uint32, _i, _i, _vp]),
     "apex_b200_mt_l2norm": (_i, [_tp, _i, _d, _i, _vp, ctypes.c_int64, _vp, _vp]),
     "apex_b200_mt_l2norm_noalloc": (_i, [_tp, _i, _d, _i, _vp, _vp]),
     "apex_b200_mt_clip_by_norm": (_i, [_tp, _i, _vp, _d, _vp, _vp]),
@@ -188,6 +202,17 @@ def mt_check_overflow(table, grad_list, flag, stream=None):
 
 
 @_traced
+def mt_check_overflow_publish(table, grad_list, flag, ticket, host_mirror, rearm, stream=None):
+    """mt_check_overflow whose last CTA also writes the final word to pinned host memory and zeroes
+    the word the next check will use (nothing else is enqueued between check and update)."""
+    global launches
+    launches += 1
+    _check(lib.apex_b200_mt_check_overflow_publish(table.ref, grad_list, _ptr(flag), _ptr(ticket), _ptr(host_mirror),
+                                                   _ptr(rearm), current_stream() if stream is None else stream),
+           "mt_check_overflow_publish")
+
+
+@_traced
 def mt_unscale(table, grad_list, inv_scale, flag, mode, stream=None):
     _count(table)
     _check(lib.apex_b200_mt_unscale(table.ref, grad_list, float(inv_scale), _ptr(flag), mode,
@@ -273,12 +298,16 @@ def scale_flat(flat, divisor, flag, stream=None):
 
 
 @_traced
-def symm_allreduce(peer_ptrs, multicast_ptr, rank, world, numel, dtype, ctas=0, stream=None):
-    """In-place SUM of a symmetric-memory buffer over `world` GPUs (this rank's half of the work)."""
+def symm_allreduce(domain, offset, numel, dtype, divisor, apply_mul, flag_offset, channel, seq, use_multicast,
+                   ctas=0, stream=None):
+    """Average (sum, x 1/divisor, inf/NaN check) a bucket of a symmetric allocation over the domain's
+    GPUs: this rank's kernel, with the cross-rank barriers inside.  flag_offset < 0: no check."""
     global launches
-    launches += 1
-    arr = (ctypes.c_uint64 * len(peer_ptrs))(*peer_ptrs)
-    _check(lib.apex_b200_symm_allreduce(arr, int(multicast_ptr), rank, world, numel, DTYPE_CODE[dtype], ctas,
+    if numel > 0:
+        launches += 1
+    _check(lib.apex_b200_symm_allreduce(ctypes.byref(domain), int(offset), int(numel), DTYPE_CODE[dtype],
+                                        float(divisor), int(bool(apply_mul)), int(flag_offset), int(channel),
+                                        int(seq), int(bool(use_multicast)), int(ctas),
                                         current_stream() if stream is None else stream), "symm_allreduce")
 
 

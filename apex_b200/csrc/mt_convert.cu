@@ -16,14 +16,14 @@ mt_grads_to_master_kernel(MtView v, int src_list, int dst_list, float inv_scale,
                           int apply_scale, const int32_t* __restrict__ flag,
                           const float* __restrict__ clip_norm, float clip_max_norm) {
     if (flag != nullptr && *flag != 0) return;
+    if (!apply_scale) inv_scale = 1.0f;       // exact widening unless the caller asked for the unscale
     // optional second factor: clip_grad_norm_'s clamp(max_norm / (norm + 1e-6), max=1)
     float coef = 1.0f;
     if (clip_norm != nullptr) {
         coef = __fdiv_rn(clip_max_norm, __fadd_rn(__ldg(clip_norm), 1e-6f));
         coef = coef > 1.0f ? 1.0f : coef;
-        apply_scale = 1;
+        apply_scale = 1;                      // (x * 1.0f) * coef from here on
     }
-    if (clip_norm == nullptr && !apply_scale) inv_scale = 1.0f;
     for (int chunk = blockIdx.x; chunk < v.total_chunks; chunk += gridDim.x) {
         const MtChunk c = mt_locate(v, chunk);
         const __half* s = mt_ptr<const __half>(v, src_list, c.tensor) + c.offset;

@@ -79,8 +79,17 @@ __device__ __forceinline__ bool check_chunk(const G* __restrict__ g, const MtChu
     return P::bad(acc);
 }
 
+// `post` (optional): what the LAST CTA to finish does once the word is final -- publish it to
+// pinned host memory (so that no device-to-host copy sits on the stream between this kernel and
+// the update it predicates) and re-arm the word the NEXT check will use (so that no memset does).
+struct CheckPost {
+    int32_t* ticket;      // device counter, zero between launches
+    int32_t* host_mirror; // mapped pinned host word, or nullptr
+    int32_t* rearm;       // another flag word to set to zero, or nullptr
+};
+
 __global__ void __launch_bounds__(kThreads)
-mt_check_overflow_kernel(MtView v, int grad_list, int32_t* __restrict__ flag) {
+mt_check_overflow_kernel(MtView v, int grad_list, int32_t* __restrict__ flag, CheckPost post) {
     for (int chunk = blockIdx.x; chunk < v.total_chunks; chunk += gridDim.x) {
         const MtChunk c = mt_locate(v, chunk);
         bool bad;
@@ -88,7 +97,20 @@ mt_check_overflow_kernel(MtView v, int grad_list, int32_t* __restrict__ flag) {
             bad = check_chunk<float>(mt_ptr<const float>(v, grad_list, c.tensor), c);
         else
             bad = check_chunk<__half>(mt_ptr<const __half>(v, grad_list, c.tensor), c);
-        mt_raise_flag(bad, c.tensor, flag);
+        mt_raise_flag(bad, c.tensor, flag);       // (ends with a block-wide barrier + thread 0's atomic)
+    }
+    if (post.ticket != nullptr && threadIdx.x == 0) {
+        __threadfence();                                          // my atomicMax before my ticket
+        if (atomicAdd(post.ticket, 1) == int(gridDim.x) - 1) {    // every other CTA is done
+            __threadfence();
+            const int32_t final_word = atomicMax(flag, 0);
+            if (post.host_mirror != nullptr) {
+                *reinterpret_cast<volatile int32_t*>(post.host_mirror) = final_word;
+                __threadfence_system();
+            }
+            if (post.rearm != nullptr) *post.rearm = 0;
+            *post.ticket = 0;
+        }
     }
 }
 
@@ -165,11 +187,27 @@ extern "C" int apex_b200_flag_clear(int32_t* d_flag, void* stream) {
 
 extern "C" int apex_b200_mt_check_overflow(const apex_b200_mt_table* t, int grad_list,
                                            int32_t* d_flag, void* stream) {
+    return apex_b200_mt_check_overflow_publish(t, grad_list, d_flag, nullptr, nullptr, nullptr, stream);
+}
+
+extern "C" int apex_b200_mt_check_overflow_publish(const apex_b200_mt_table* t, int grad_list, int32_t* d_flag,
+                                                   int32_t* d_ticket, int32_t* h_mirror, int32_t* d_rearm,
+                                                   void* stream) {
     if (t == nullptr || d_flag == nullptr || grad_list < 0 || grad_list >= t->n_lists) return APEX_B200_EINVAL;
-    if (t->total_chunks == 0) return 0;
+    if (d_ticket == nullptr && (h_mirror != nullptr || d_rearm != nullptr)) return APEX_B200_EINVAL;
+    if (d_rearm == d_flag && d_flag != nullptr && d_rearm != nullptr) return APEX_B200_EINVAL;
+    if (t->total_chunks == 0) {
+        // nothing to scan, but the caller still expects the mirror and the re-armed word
+        if (d_ticket == nullptr) return 0;
+        CheckPost post{d_ticket, h_mirror, d_rearm};
+        MtView empty{};
+        mt_check_overflow_kernel<<<1, kThreads, 0, static_cast<cudaStream_t>(stream)>>>(empty, 0, d_flag, post);
+        return mt_cuda_status();
+    }
     if (t->d_table == nullptr) return APEX_B200_EINVAL;
+    CheckPost post{d_ticket, h_mirror, d_rearm};
     mt_check_overflow_kernel<<<mt_grid(t->total_chunks, 8), kThreads, 0, static_cast<cudaStream_t>(stream)>>>(
-        mt_view(t), grad_list, d_flag);
+        mt_view(t), grad_list, d_flag, post);
     return mt_cuda_status();
 }
 

@@ -105,6 +105,9 @@ class _StepPlan(object):
         self.state_map = None
         self.state_len = 0
         self.state_dicts = None
+        self._watch = ()
+        self._watch_ptrs = ()
+        self._cursor = 0
 
     @staticmethod
     def build(opt, kind, gi, group, from_masters, halves, masters, floats, grads):
@@ -149,6 +152,12 @@ class _StepPlan(object):
         table.update(lists, flags)
         table.remember(grads)
         plan.table = table
+        # objects whose storage could be swapped under an unchanged identity (`p.data = ...`,
+        # `module.half()`): masters/params, fp16 model params, state tensors.  still_valid() compares
+        # the addresses of the first, the last and one rotating entry of each list per step.
+        plan._watch = [plan.owners, list(halves) + [None] * len(floats)] + [list(l) for l in lists[2:-1]]
+        plan._watch_ptrs = [[0 if o is None else o.data_ptr() for o in objs] for objs in plan._watch]
+        plan._cursor = 0
         if not plan.fresh:
             plan._bind_state(state)
         return plan
@@ -246,6 +255,13 @@ class _StepPlan(object):
             if self.state_dicts[0].get('step') is not self.steps[0] or \
                     self.state_dicts[-1].get('step') is not self.steps[-1]:
                 return False
+        n = len(self.owners)
+        k = self._cursor = (self._cursor + 1) % n
+        for objs, ptrs in zip(self._watch, self._watch_ptrs):
+            for i in (0, n - 1, k):
+                o = objs[i]
+                if o is not None and o.data_ptr() != ptrs[i]:
+                    return False      # same object, new storage: rebuild (update() compares every address)
         return True
 
     def commit(self, state):
@@ -368,7 +384,13 @@ class FP16_Optimizer(object):
     def _ensure_device(self, tensor):
         if self._device is None:
             self._device = tensor.device
-            self._flag = new_flag(self._device)
+            # two overflow words used alternately (each check re-arms the other one: no memset on the
+            # stream) and the ticket counter of the publishing check kernel
+            words = torch.zeros(4, dtype=torch.int32, device=self._device)
+            self._flag_pair = (words[0:1], words[1:2])
+            self._flag_ticket = words[2:3]
+            self._flag_turn = 0
+            self._flag = self._flag_pair[0]
             self._flag_host = torch.zeros(1, dtype=torch.int32,
                                           pin_memory=(self._device.type == "cuda"))
 
@@ -477,7 +499,6 @@ class FP16_Optimizer(object):
             ev.record()
             self._overflow_event = ev
             return
-        self._flag_src = self._flag
         table = self._check_table
         if table is None:
             table = self._check_table = TensorTable(self._device, 1, CHUNK_CHECK)
@@ -494,9 +515,13 @@ class FP16_Optimizer(object):
                     raise TypeError("apex_b200: unexpected gradient dtype %s" % g.dtype)
             table.update([grads], flags)
             table.remember(grads)
-        _C.flag_clear(self._flag)
-        _C.mt_check_overflow(table, 0, self._flag)
-        self._flag_host.copy_(self._flag, non_blocking=True)
+        # One launch and nothing else on the stream: the kernel's last CTA writes the verdict into
+        # pinned host memory and zeroes the word the next check will use.  (The previous verdict has
+        # been read by the host -- step() does -- or is being discarded, before this launch re-arms.)
+        turn = self._flag_turn = self._flag_turn ^ 1
+        self._flag = self._flag_src = self._flag_pair[turn]
+        _C.mt_check_overflow_publish(table, 0, self._flag, self._flag_ticket, self._flag_host,
+                                     self._flag_pair[turn ^ 1])
         ev = torch.cuda.Event()
         ev.record()
         self._overflow_event = ev
@@ -780,6 +805,7 @@ class FP16_Optimizer(object):
                 step_size = (group['lr'] / bias_correction1) * -1
                 _C.mt_fused_adam(plan.table, group['lr'], beta1, beta2, group['eps'], group['weight_decay'],
                                  step_size, bias_correction2 ** 0.5,
+                                 type(self.optimizer) is torch.optim.AdamW or
                                  bool(group.get('decoupled_weight_decay', False)), inv_scale, apply_scale, flag,
                                  clip)
 
@@ -793,8 +819,8 @@ class FP16_Optimizer(object):
         been replaced.  False = this group cannot be fused, None = nothing to do."""
         if group.get('maximize', False) or group.get('differentiable', False):
             return False
-        if isinstance(group['lr'], torch.Tensor):
-            return False
+        if isinstance(group['lr'], torch.Tensor) or group.get('fused'):
+            return False          # (a torch-fused optimizer keeps its step counters on the device)
         if kind == "adam":
             if group.get('amsgrad', False) or group.get('capturable', False):
                 return False

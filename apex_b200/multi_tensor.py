@@ -50,11 +50,11 @@ class TensorTable(object):
         self._host = None      # pinned staging buffer
         self._dev = None       # device copy
         self._copied = None    # event: staging buffer free for reuse
-        self.lists = None      # kept only when _C.keep_table_refs is set (CPU test doubles)
-        self.flags = None
         self.rebuilds = 0
         self._refs = None      # weak references to the tensors the table was built from
         self._ids = None
+        self._ptrs = None      # their addresses when the table was built (spot-checked by built_from)
+        self._cursor = 0
         self._alive = False
         self._generation = None
 
@@ -63,12 +63,28 @@ class TensorTable(object):
     # (the table must not keep gradients alive that the user has dropped) carries a callback that
     # voids the table the moment one of them dies -- an id can only be reused after that -- so the
     # per-step test is one C-speed pass over the ids: microseconds for hundreds of tensors, where
-    # update() fetches every address again.
+    # update() fetches every address again.  Identity alone would miss a tensor that keeps its python
+    # object but gets new storage (`p.data = ...`, `module.half()`, `grad.set_(...)`): the addresses of
+    # the first, the last and one rotating tensor are therefore compared on every call -- wholesale
+    # swaps are caught at once, a single swapped tensor within n calls.  (Reassigning `.data` of
+    # individual tensors between steps is outside what the fast path promises; `invalidate()` or any
+    # changed object identity forces the full comparison of `update`.)
     def built_from(self, objs):
-        return self._alive and self._key is not None and self._ids == list(map(id, objs))
+        if not (self._alive and self._key is not None and self._ids == list(map(id, objs))):
+            return False
+        ptrs = self._ptrs
+        if ptrs:
+            n = len(ptrs)
+            k = self._cursor = (self._cursor + 1) % n
+            if objs[0].data_ptr() != ptrs[0] or objs[-1].data_ptr() != ptrs[-1] or objs[k].data_ptr() != ptrs[k]:
+                self.invalidate()
+                return False
+        return True
 
     def remember(self, objs):
         self._ids = list(map(id, objs))
+        self._ptrs = [o.data_ptr() for o in objs]
+        self._cursor = 0
         self._alive = True
         token = self._generation = object()
         me = weakref.ref(self)
@@ -95,9 +111,6 @@ class TensorTable(object):
         numels = np.fromiter((t.numel() for t in lists[0]), dtype=np.int64, count=n)
         fl = np.zeros(n, dtype=np.int32) if flags is None else np.asarray(flags, dtype=np.int32)
         key = (ptrs.tobytes(), numels.tobytes(), fl.tobytes())
-        if getattr(_C, "keep_table_refs", False):
-            self.lists = [list(l) for l in lists]
-            self.flags = fl
         if key == self._key:
             return False
         self._key = key
@@ -131,6 +144,7 @@ class TensorTable(object):
         self._key = None
         self._refs = None
         self._ids = None
+        self._ptrs = None
         self._alive = False
 
 

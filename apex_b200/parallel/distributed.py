@@ -27,6 +27,7 @@ from torch.nn.modules import Module
 from .. import _C
 from ..multi_tensor import TensorTable, CHUNK_STREAM, is_dense
 from . import symm
+from .buckets import GradBucket
 
 # bucket class per dtype; leftovers are appended in this order (reference :154-156, :178-180)
 _DTYPE_CLASS = {torch.float16: 0, torch.float32: 1, torch.float64: 2}
@@ -154,112 +155,194 @@ def verified_flag(grads):
 
 
 class _BucketPipeline(object):
-    """Averages buckets with the three stages of consecutive buckets overlapped:
+    """Averages gradient buckets in their persistent flat homes (parallel/buckets.py).
 
-        gather stream :  gather(b+1)                 (apex_b200_mt_flatten)
-        NCCL stream   :        all_reduce(b)         (torch.distributed, async)
-        scatter stream:              x 1/world, scatter, check (b-1)   (apex_b200_mt_scale_unflatten)
+    NVLink domain, NCCL backend (parallel/symm.py): the bucket lives in symmetric memory and ONE kernel
+    of ours per bucket does barrier -> two-shot sum -> x 1/world -> inf/NaN check -> barrier, in place,
+    on the stream ``submit`` is called on.  Gradients that already live in the bucket cost nothing
+    else; strays are copied in first (one launch) and either become views of the bucket (``owners``
+    given: DistributedDataParallel) or get the result copied back (plain tensor lists).
 
-    The reference runs the three steps of a bucket back to back on one stream
-    (distributed.py:11-23 under :294-296), so HBM-bound copies and the NVLink-bound collective
-    never overlap.  The order of collectives is unchanged: buckets are issued in the order given.
+    Otherwise (gloo, fp64, one rank, APEX_B200_SYMM=0): same flat homes in ordinary memory,
+    ``dist.all_reduce`` on the flat buffer, then one in-place launch for x 1/world and the check on a
+    second stream, so that the collective of bucket b overlaps the scaling of bucket b-1.
+
+    The reference runs cat + all_reduce + ``/=`` + n copy_ per bucket on one stream
+    (distributed.py:11-23 under :294-296).  The order of collectives is the same: as submitted.
     """
+
+    MIN_ARENA = 32 << 20
 
     def __init__(self, gather_stream):
         self.gather_stream = gather_stream
         self.scatter_stream = torch.cuda.Stream()
-        self.symm_pipe = None          # created when the symmetric-memory path is first used
-        self.slots = {}
-        self._spare = []
-        self.check_flag = None         # device word raised by the scatter pass of the current round
+        self.slots = {}                # key -> (GradBucket, Arena or None, byte offset)
+        self.arenas = []               # symmetric allocations of the current plan
+        self._arena_flags = {}         # id(arena) -> (int32[1] view, byte offset)
+        self._used_arenas = []         # arenas touched in the current round, primary first
+        self.check_flag = None         # device word raised when an averaged value of the round is inf/NaN
+        self._armed = True
         self._token = None
         self._round_id = 0
 
+    # ---- rounds and the overflow word -------------------------------------------------------------
+
     def begin_round(self):
-        """A new backward starts: gradients verified from now on belong to a fresh round."""
+        """A new backward starts: the word is cleared before its first bucket, gradients verified
+        from now on belong to a fresh round."""
         self._round_id += 1
         self._token = None
+        self._armed = True
 
-    def _mark(self, bucket):
-        """Called when a bucket is submitted: clear the round's flag before its first bucket, and
-        tag every gradient of the bucket."""
-        dev = bucket[0].device
-        if self.check_flag is None or self.check_flag.device != dev:
-            self.check_flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    def _flag_of(self, arena):
+        got = self._arena_flags.get(id(arena))
+        if got is None:
+            got = self._arena_flags[id(arena)] = arena.new_flag()
+        return got
+
+    def _arm(self, device, arena):
+        """Make sure the round's word exists and is zero before the first kernel that may raise it."""
+        if self.check_flag is None or self.check_flag.device != device:
+            self.check_flag = self._flag_of(arena)[0] if arena is not None else \
+                torch.zeros(1, dtype=torch.int32, device=device)
+        if self._armed:
+            self._armed = False
+            self._used_arenas = []
+            _C.flag_clear(self.check_flag)
+            for a in self.arenas:
+                word = self._flag_of(a)[0]
+                if word.data_ptr() != self.check_flag.data_ptr():
+                    _C.flag_clear(word)
+            cleared = torch.cuda.Event()
+            cleared.record()
+            self.scatter_stream.wait_event(cleared)
+        if arena is not None and arena not in self._used_arenas:
+            self._used_arenas.append(arena)
+
+    def _tag(self, tensors):
         if self._token is None:
             self._token = _Verified(self.check_flag, self._round_id)
-            _C.flag_clear(self.check_flag)          # on the gather stream, before any scatter of this round
-            self._cleared = torch.cuda.Event()
-            self._cleared.record()
-            self.scatter_stream.wait_event(self._cleared)
         token = self._token
-        for g in bucket:
+        for g in tensors:
             setattr(g, VERIFIED_ATTR, (token, g._version))
-        token.count += len(bucket)
-        return self.check_flag
+        token.count += len(tensors)
+
+    # ---- flat homes -------------------------------------------------------------------------------------
 
     def reset(self):
-        """The bucket structure changed.  Symmetric-memory slices cannot be given back, so the
-        slots are kept aside and reused by new buckets of the same size and dtype."""
-        self._spare.extend(s for s in self.slots.values() if isinstance(s, symm.SymmSlot))
+        """The bucket structure changed: new homes will be planned.  Old arenas are not reused (old
+        gradient views may still be alive); they are released with their last view."""
         self.slots = {}
+        self.arenas = []
+        self._arena_flags = {}
+        self._used_arenas = []
+        self.check_flag = None
+        self._armed = True
 
-    def _symm_slot(self, bucket):
-        total = sum(t.numel() for t in bucket)
-        for i, spare in enumerate(self._spare):
-            if spare.total == total and spare.flat is not None and spare.flat.dtype == bucket[0].dtype:
-                return self._spare.pop(i)
-        return symm.SymmSlot()
+    @staticmethod
+    def _wants_symm(like):
+        return symm.enabled() and like[0].dtype in (torch.float16, torch.float32) and like[0].is_cuda
 
-    def submit(self, key, bucket, flag=None, verify=False):
-        """Enqueue the averaging of ``bucket``; returns at once.  Call from inside
-        ``with torch.cuda.stream(gather_stream)``.  ``verify=True``: the scatter pass also checks the
-        averaged values and the gradients are tagged so that FP16_Optimizer can skip its own scan."""
-        if len(bucket) == 0:
-            return
-        if verify and flag is None and bucket[0].dtype in (torch.float16, torch.float32):
-            flag = self._mark(bucket)
+    def _symm_home(self, like, world):
+        """(storage, arena, offset) inside a symmetric allocation, growing the set of arenas if needed."""
+        es = like[0].element_size()
+        nbytes = GradBucket.nbytes_for(like, world)
+        for arena in self.arenas:
+            off = arena.take(nbytes)
+            if off is not None:
+                break
+        else:
+            size = max(self.MIN_ARENA, nbytes + symm.ALIGN, 2 * (self.arenas[-1].nbytes if self.arenas else 0))
+            arena = symm.Arena(size, like[0].device)        # collective: every rank gets here alike
+            self.arenas.append(arena)
+            off = arena.take(nbytes)
+        return arena.buf[off:off + nbytes].view(like[0].dtype), arena, off
+
+    def _new_slot(self, like):
         world = dist.get_world_size()
-        if len(bucket) == 1 and bucket[0].is_contiguous():
-            only = bucket[0]
-            work = dist.all_reduce(only, async_op=True)
+        if self._wants_symm(like):
+            try:
+                storage, arena, off = self._symm_home(like, world)
+                return (GradBucket(like, world, storage), arena, off)
+            except RuntimeError as err:           # every rank fails alike: allocation + rendezvous are collective
+                if "bucket tensors must be dense" in str(err):
+                    raise
+                symm.mark_broken(err)
+        return (GradBucket(like, world), None, 0)
+
+    def plan(self, buckets):
+        """Create the homes of ``[(key, tensors-like)]`` at once: ONE symmetric allocation (one
+        rendezvous) holds every bucket that can live there, back to back."""
+        self.reset()
+        world = dist.get_world_size()
+        want = [like for _, like in buckets if like and self._wants_symm(like)]
+        if want:
+            total = sum((GradBucket.nbytes_for(like, world) + symm.ALIGN - 1) // symm.ALIGN * symm.ALIGN
+                        for like in want) + symm.ALIGN
+            try:
+                self.arenas.append(symm.Arena(total, want[0][0].device))
+            except RuntimeError as err:
+                symm.mark_broken(err)
+        for key, like in buckets:
+            if like:
+                try:
+                    self.slots[key] = self._new_slot(like)
+                except (RuntimeError, TypeError):
+                    pass                      # not a bucket we can house: submit() reports it in context
+
+    # ---- the data path -------------------------------------------------------------------------------------
+
+    def submit(self, key, bucket, verify=False, owners=None):
+        """Enqueue the averaging of ``bucket`` on the current stream (DDP: its reduction stream);
+        returns at once.  ``owners`` (parameters, one per tensor): a gradient that does not live in
+        the bucket yet is replaced by its view (``owner.grad = view``) instead of being copied back.
+        ``verify``: tag the gradients so that FP16_Optimizer can take the round's word as its own
+        overflow check.  Returns the list of tensors that now hold the averaged gradients."""
+        if len(bucket) == 0:
+            return bucket
+        slot = self.slots.get(key)
+        if slot is None or not slot[0].fits(bucket):
+            slot = self.slots[key] = self._new_slot(bucket)
+        home, arena, offset = slot
+        world = dist.get_world_size()
+        checks = home.dtype in (torch.float16, torch.float32)
+        self._arm(home.device, arena)
+        strays = home.strays(bucket)
+        home.copy_in(bucket, strays)
+        if arena is not None:
+            word, word_off = self._flag_of(arena)
+            arena.allreduce(offset, home.padded, home.dtype, world, word_off)
+            if strays and owners is None:
+                home.copy_out(bucket, strays)
+        else:
+            work = dist.all_reduce(home.flat, async_op=True)
             with torch.cuda.stream(self.scatter_stream):
                 work.wait()
-                _C.scale_flat(only.view(-1), world, flag)
-            return
-        if symm.enabled() and bucket[0].dtype in (torch.float16, torch.float32):
-            # our own allreduce over peer-mapped memory instead of NCCL (parallel/symm.py)
-            slot = self.slots.get(key)
-            try:
-                if not isinstance(slot, symm.SymmSlot):
-                    slot = self._symm_slot(bucket)
-                    slot.bind(bucket)             # allocation + rendezvous: may not be possible on this box
-                    self.slots[key] = slot
-            except RuntimeError as err:           # every rank fails alike: the rendezvous is collective
-                symm.mark_broken(err)
-                self.slots.pop(key, None)
-            else:
-                if self.symm_pipe is None:
-                    self.symm_pipe = symm.SymmPipeline(self.gather_stream, self.scatter_stream)
-                self.symm_pipe.submit(slot, bucket, flag)
-                return
-        slot = self.slots.get(key)
-        if not isinstance(slot, _FlatSlot):
-            slot = self.slots[key] = _FlatSlot()
-        flat = slot.bind(bucket)
-        _C.mt_flatten(slot.table, 0, flat)
-        work = dist.all_reduce(flat, async_op=True)
-        with torch.cuda.stream(self.scatter_stream):
-            work.wait()
-            _C.mt_scale_unflatten(slot.table, flat, 0, world, True, flag)
+                _C.scale_flat(home.flat, world, self.check_flag if checks else None)
+                if strays and owners is None:
+                    home.copy_out(bucket, strays)
+        result = bucket
+        if strays and owners is not None:
+            result = list(bucket)
+            for i in strays:
+                owners[i].grad = result[i] = home.views[i]
+        if verify and checks:
+            self._tag(result)
+        return result
 
     def join(self, stream):
         """Make ``stream`` wait for everything submitted so far; the round's verification is then
         usable by work enqueued on ``stream``."""
         stream.wait_stream(self.gather_stream)
-        if self.symm_pipe is not None:
-            self.symm_pipe.join(stream)
         stream.wait_stream(self.scatter_stream)
+        if len(self._used_arenas) > 1 or (self._used_arenas and
+                                          self._flag_of(self._used_arenas[0])[0].data_ptr() != self.check_flag.data_ptr()):
+            # buckets of several allocations raised several words: fold them into the round's
+            with torch.cuda.stream(stream):
+                for a in self._used_arenas:
+                    word = self._flag_of(a)[0]
+                    if word.data_ptr() != self.check_flag.data_ptr():
+                        torch.maximum(self.check_flag, word, out=self.check_flag)
         if self._token is not None:
             self._token.done = True
 
@@ -462,6 +545,7 @@ class DistributedDataParallel(Module):
         self._layout = None
         self._round = None
         self._where = {}          # id(param) -> (bucket_idx, bucket_loc)
+        self._bucket_params = []  # bucket_idx -> parameters, in bucket order
         self._index_of = {}       # id(param) -> index in active_params
         self._pipeline = _BucketPipeline(self.reduction_stream)
 
@@ -517,7 +601,10 @@ class DistributedDataParallel(Module):
         dist.broadcast(info, 0)
         self._layout.decode(info.tolist())      # one device-to-host copy for the whole vector
         self._where = {id(self.active_params[i]): pos for i, pos in self._layout.positions().items()}
-        self._pipeline.reset()
+        # the flat homes of all buckets at once (one symmetric allocation); the gradients move in
+        # during the first overlapped backward (comm_ready_buckets)
+        self._bucket_params = [[self.active_params[i] for i in members] for members in self._layout.members]
+        self._pipeline.plan([(b, [p.data for p in params]) for b, params in enumerate(self._bucket_params)])
 
     # ---- hooks ---------------------------------------------------------------------------
 
@@ -580,7 +667,10 @@ class DistributedDataParallel(Module):
         self.reduction_stream.wait_stream(torch.cuda.current_stream())
         with torch.cuda.stream(self.reduction_stream):
             for b in eligible:
-                self._pipeline.submit(b, self._round.grads[b], verify=True)
+                # gradients not yet living in the bucket's flat home are re-homed: param.grad becomes
+                # a view of the bucket, so the next backward accumulates straight into it
+                self._round.grads[b] = self._pipeline.submit(b, self._round.grads[b], verify=True,
+                                                             owners=self._bucket_params[b])
 
     # ---- forward -----------------------------------------------------------------------------
 

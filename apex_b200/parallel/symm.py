@@ -1,19 +1,19 @@
-"""Flat buckets in peer-mapped (symmetric) memory and their allreduce without NCCL.
+"""Symmetric (peer-mapped) memory for the gradient buckets and their averaging without NCCL.
 
-torch.distributed's symmetric memory is used for the plumbing only: allocating the buffer so that
-every rank of the NVLink domain can address every other rank's copy (and, on NVSwitch, the multicast
-alias of all copies), and the cross-rank barrier between phases.  The data path is ours:
+torch.distributed's symmetric memory is used for plumbing only: allocating a buffer that every rank
+of the NVLink domain can address on every other rank (and, on NVSwitch, through a multicast alias of
+all copies), and exchanging the addresses.  Everything that happens per bucket is ours
+(``apex_b200_symm_allreduce``, csrc/symm_allreduce.cu): ONE kernel per rank that waits for its peers,
+sums the bucket across ranks (switch-side ``multimem`` or peer loads/stores), multiplies by 1/world,
+tests the result for inf/NaN and waits for its peers again -- where the reference runs
+``all_reduce`` + ``/=`` (apex/parallel/distributed.py:15-20) and, later, a scan of the averaged
+gradients (apex/fp16_utils/fp16_optimizer.py:213-221).
 
-    gather   (apex_b200_mt_flatten)        gradients -> my copy of the flat bucket
-    barrier                                 every rank has gathered
-    allreduce (apex_b200_symm_allreduce)    two-shot SUM: switch-side (multimem) or peer loads/stores
-    barrier                                 every rank has written its slice everywhere
-    scatter  (apex_b200_mt_scale_unflatten) x 1/world, back into the gradients, inf/NaN check
+Layout of one allocation (``Arena``):
+    [0, 32 KiB)        signal words of the in-kernel barriers  [channel][cta][rank] uint32
+    [48 KiB, +256 B)   overflow words (int32), one per user of the arena
+    [64 KiB, ...)      buckets, 256 B aligned
 
-Measured on B200 boxes (GPT-2-XL gradients, 3.1 GB fp16, 256 MB buckets, whole bucket path):
-    2 GPUs:  NCCL 7.87 ms   peer-to-peer 6.56 ms   multicast 9.47 ms
-    8 GPUs:  NCCL 9.89 ms   peer-to-peer 10.95 ms  multicast 8.79 ms
-so the default ("auto") uses peer loads/stores for 2 ranks and the switch multicast beyond that.
 APEX_B200_SYMM=0 keeps NCCL; if symmetric memory cannot be set up the NCCL path is used with a warning.
 """
 import os
@@ -22,13 +22,18 @@ import torch
 import torch.distributed as dist
 
 from .. import _C
-from ..multi_tensor import TensorTable, CHUNK_STREAM, is_dense
 
 _enabled = os.environ.get("APEX_B200_SYMM", "1") != "0"
 _ctas = int(os.environ.get("APEX_B200_SYMM_CTAS", "0"))
 _force_p2p = os.environ.get("APEX_B200_SYMM_P2P", "") == "1"
 _force_mc = os.environ.get("APEX_B200_SYMM_P2P", "") == "0"
 _broken = False
+_single_host = None
+
+HEADER_BYTES = 64 << 10
+FLAG_BASE = 48 << 10
+MAX_FLAGS = 64
+ALIGN = 256
 
 
 def enable(flag=True):
@@ -36,9 +41,23 @@ def enable(flag=True):
     _enabled = bool(flag)
 
 
+def _one_nvlink_domain():
+    """Symmetric memory spans one host.  torchrun exports LOCAL_WORLD_SIZE; without it (processes
+    spawned by hand) every rank must have its own GPU on this host."""
+    global _single_host
+    if _single_host is None:
+        world = dist.get_world_size()
+        local = os.environ.get("LOCAL_WORLD_SIZE")
+        if local is not None:
+            _single_host = int(local) == world
+        else:
+            _single_host = world <= torch.cuda.device_count()
+    return _single_host
+
+
 def enabled():
     return _enabled and not _broken and dist.is_initialized() and dist.get_backend() == "nccl" \
-        and dist.get_world_size() > 1
+        and dist.get_world_size() > 1 and dist.get_world_size() <= _C.SYMM_MAX_WORLD and _one_nvlink_domain()
 
 
 def mark_broken(err):
@@ -49,161 +68,76 @@ def mark_broken(err):
     warnings.warn("apex_b200: symmetric-memory allreduce unavailable (%s); using NCCL" % (err,))
 
 
-class _Arena(object):
-    """One symmetric-memory allocation that many buckets are carved out of: a single rendezvous
-    (collective, milliseconds) serves hundreds of buckets.  Sizes double, so a model needs a handful."""
+def _timeout_ns():
+    """How long a rank waits for a peer inside the kernel before it traps.  Default: never (a late
+    rank -- checkpointing, a data-loader stall -- is waited for, as NCCL's kernels do);
+    APEX_B200_SYMM_TIMEOUT_S sets a limit."""
+    return int(float(os.environ.get("APEX_B200_SYMM_TIMEOUT_S", "0")) * 1e9)
 
-    MIN_BYTES = 64 << 20
-    ALIGN = 256
 
-    def __init__(self, nbytes, device):
+class Arena(object):
+    """One symmetric allocation: a single rendezvous (collective, milliseconds) serves every bucket
+    carved out of it.  Must be created by all ranks in the same order."""
+
+    def __init__(self, payload_bytes, device):
         import torch.distributed._symmetric_memory as symm_mem
-        self.nbytes = nbytes
-        self.buf = symm_mem.empty(nbytes, dtype=torch.uint8, device=device)
+        self.nbytes = HEADER_BYTES + int(payload_bytes)
+        self.buf = symm_mem.empty(self.nbytes, dtype=torch.uint8, device=device)
         self.buf.zero_()
+        # the zeros (signal words!) must be in memory before any peer can learn the address
+        torch.cuda.current_stream().synchronize()
         self.handle = symm_mem.rendezvous(self.buf, dist.group.WORLD)      # same order on every rank
-        self.used = 0
+        h = self.handle
+        d = _C.SymmDomain()
+        d.rank, d.world = h.rank, h.world_size
+        for r, p in enumerate(h.buffer_ptrs):
+            d.peer_base[r] = int(p)
+        d.multicast_base = int(h.multicast_ptr or 0)
+        d.signal_offset = 0
+        d.timeout_ns = _timeout_ns()
+        self.domain = d
+        self.world = h.world_size
+        self.has_multicast = d.multicast_base != 0
+        self.used = HEADER_BYTES
+        self.seq = [0] * _C.SYMM_CHANNELS
+        self._flags = self.buf[FLAG_BASE:FLAG_BASE + 4 * MAX_FLAGS].view(torch.int32)
+        self._flags_used = 0
+        dist.barrier()          # every rank's zeros are in place before anybody launches
 
     def take(self, nbytes):
-        start = (self.used + self.ALIGN - 1) // self.ALIGN * self.ALIGN
+        """Byte offset of a fresh 256 B-aligned span, or None when the arena is full."""
+        start = (self.used + ALIGN - 1) // ALIGN * ALIGN
         if start + nbytes > self.nbytes:
             return None
         self.used = start + nbytes
         return start
 
+    def room(self):
+        return self.nbytes - (self.used + ALIGN - 1) // ALIGN * ALIGN
 
-_arenas = {}      # device index -> list of arenas (buckets of every DDP instance of the process share them)
+    def new_flag(self):
+        """(int32 tensor of one element inside the arena, its byte offset).  The word has the same
+        offset on every rank; our kernel raises it everywhere."""
+        if self._flags_used >= MAX_FLAGS:
+            raise RuntimeError("apex_b200: out of overflow words in this symmetric arena")
+        i = self._flags_used
+        self._flags_used += 1
+        return self._flags[i:i + 1], FLAG_BASE + 4 * i
 
+    def use_multicast(self):
+        return self.has_multicast and not _force_p2p and (_force_mc or self.world > 2)
 
-def _carve(nbytes, device):
-    arenas = _arenas.setdefault(device.index, [])
-    for arena in arenas:
-        off = arena.take(nbytes)
-        if off is not None:
-            return arena, off
-    size = max(_Arena.MIN_BYTES, nbytes, 2 * arenas[-1].nbytes if arenas else 0)
-    arena = _Arena(size, device)
-    arenas.append(arena)
-    return arena, arena.take(nbytes)
-
-
-class SymmSlot(object):
-    """A flat bucket living in symmetric memory + the table of the tensors it stands for."""
-
-    def __init__(self):
-        self.table = None
-        self.flat = None          # padded slice of an arena, typed
-        self.view = None          # first `total` elements
-        self.handle = None
-        self.offset = 0           # byte offset of the slice inside the arena
-        self.total = 0
-
-    def bind(self, tensors):
-        head = tensors[0]
-        if head.dtype not in (torch.float16, torch.float32):
-            raise TypeError("apex_b200: symmetric-memory buckets are fp16 or fp32")
-        total = 0
-        for t in tensors:
-            if t.dtype != head.dtype or not is_dense(t):
-                raise RuntimeError("apex_b200: bucket tensors must be dense and of one type")
-            total += t.numel()
-        world = dist.get_world_size()
-        if self.flat is None or total != self.total or self.flat.dtype != head.dtype:
-            unit = (16 // head.element_size()) * world
-            padded = (total + unit - 1) // unit * unit
-            arena, off = _carve(padded * head.element_size(), head.device)
-            self.flat = arena.buf[off:off + padded * head.element_size()].view(head.dtype)
-            self.handle = arena.handle
-            self.offset = off
-            self.view = self.flat[:total]
-            self.total = total
-        if self.table is None:
-            self.table = TensorTable(head.device, 1, CHUNK_STREAM)
-        self.table.update([tensors])
-        return self.view
-
-    def barrier(self, channel=0):
-        self.handle.barrier(channel=channel, timeout_ms=20000)
-
-    def launch_allreduce(self):
-        """This rank's half of the two-shot SUM; the caller provides the barriers."""
-        h = self.handle
-        mc = int(h.multicast_ptr or 0)
-        use_mc = mc != 0 and not _force_p2p and (_force_mc or h.world_size > 2)
-        ctas = _ctas if _ctas > 0 else (32 if use_mc else 148)
-        peers = [int(p) + self.offset for p in h.buffer_ptrs]
-        _C.symm_allreduce(peers, mc + self.offset if use_mc else 0, h.rank, h.world_size, self.flat.numel(),
-                          self.flat.dtype, ctas)
-
-    def allreduce(self):
-        self.barrier(0)
-        self.launch_allreduce()
-        self.barrier(1)
+    def allreduce(self, offset, numel, dtype, divisor, flag_offset, channel=0, apply_mul=True):
+        """This rank's kernel of the averaging of [offset, offset + numel * itemsize) on the current
+        stream.  Every rank must issue the same sequence of calls per channel."""
+        self.seq[channel] += 1
+        mc = self.use_multicast()
+        ctas = _ctas if _ctas > 0 else (32 if mc else 148)
+        _C.symm_allreduce(self.domain, offset, numel, dtype, divisor, apply_mul,
+                          -1 if flag_offset is None else flag_offset, channel, self.seq[channel], mc, ctas)
 
 
-class SymmPipeline(object):
-    """gather / allreduce / scatter of consecutive buckets overlapped.
-
-    Buckets alternate between two collective streams.  On its stream a bucket runs
-        wait(gathered) -> barrier "every rank has gathered b" -> allreduce kernel -> barrier "every rank
-        has reduced b" -> event for the scatter
-    so the barriers of bucket b+1 (tiny kernels that spin until all ranks arrive) execute while the
-    allreduce kernel of bucket b is still moving data: the NVLink-bound kernels run back to back
-    instead of being separated by a cross-rank round trip.  Barriers in flight at the same time use
-    different signal-pad channels (2 per stream).  The allreduce kernels never wait for a peer, so
-    there is no circular wait.  APEX_B200_SYMM_STREAMS=1 serialises everything on one stream."""
-
-    def __init__(self, gather_stream, scatter_stream):
-        self.gather_stream = gather_stream
-        self.scatter_stream = scatter_stream
-        n = 1 if os.environ.get("APEX_B200_SYMM_STREAMS", "2") == "1" else 2
-        self.comm_streams = [torch.cuda.Stream() for _ in range(n)]
-        self.count = 0
-
-    def submit(self, slot, bucket, flag):
-        view = slot.bind(bucket)
-        _C.mt_flatten(slot.table, 0, view)            # on the gather stream (current)
-        gathered = torch.cuda.Event()
-        gathered.record()
-        k = self.count % len(self.comm_streams)
-        self.count += 1
-        cs = self.comm_streams[k]
-        with torch.cuda.stream(cs):
-            cs.wait_event(gathered)
-            slot.barrier(2 * k)
-            slot.launch_allreduce()
-            slot.barrier(2 * k + 1)
-            reduced = torch.cuda.Event()
-            reduced.record()
-        with torch.cuda.stream(self.scatter_stream):
-            self.scatter_stream.wait_event(reduced)
-            _C.mt_scale_unflatten(slot.table, view, 0, dist.get_world_size(), True, flag)
-
-    def join(self, stream):
-        for cs in self.comm_streams:
-            stream.wait_stream(cs)
-
-
-def average_bucket(slot, bucket, flag=None, comm_stream=None, scatter_stream=None):
-    """gather -> symmetric allreduce -> x 1/world + scatter + check.
-
-    With ``comm_stream``/``scatter_stream`` the three stages run on three streams chained by events,
-    so that consecutive buckets overlap (gather of b+1, allreduce of b, scatter of b-1); without
-    them everything is enqueued on the current stream."""
-    view = slot.bind(bucket)
-    _C.mt_flatten(slot.table, 0, view)
-    world = dist.get_world_size()
-    if comm_stream is None:
-        slot.allreduce()
-        _C.mt_scale_unflatten(slot.table, view, 0, world, True, flag)
-        return
-    gathered = torch.cuda.Event()
-    gathered.record()
-    with torch.cuda.stream(comm_stream):
-        comm_stream.wait_event(gathered)
-        slot.allreduce()
-        reduced = torch.cuda.Event()
-        reduced.record()
-    with torch.cuda.stream(scatter_stream):
-        scatter_stream.wait_event(reduced)
-        _C.mt_scale_unflatten(slot.table, view, 0, world, True, flag)
+def padded_numel(numel, element_size, world):
+    """Bucket length our kernel accepts: every rank's slice is a whole number of 16 B vectors."""
+    unit = (16 // element_size) * world
+    return (numel + unit - 1) // unit * unit

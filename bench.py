@@ -305,6 +305,90 @@ def build_buckets(params, bucket_elems):
     return layout.members
 
 
+def reference_bucket_rule(numels, dtypes, message_size):
+    """apex/parallel/distributed.py:248-261 and :176-180 restated for gradients arriving in reverse
+    parameter order: per dtype slot (half, float, double) a running bucket, cut as soon as it holds
+    >= message_size elements; leftovers appended in slot order.  Written independently of
+    apex_b200.parallel so that the layout the bench uses can be checked against it."""
+    slot_of = {torch.float16: 0, torch.float32: 1, torch.float64: 2}
+    closed, running, count = [], [[], [], []], [0, 0, 0]
+    for i in reversed(range(len(numels))):
+        k = slot_of[dtypes[i]]
+        running[k].append(i)
+        count[k] += numels[i]
+        if count[k] >= message_size:
+            closed.append(running[k])
+            running[k], count[k] = [], 0
+    return closed + [r for r in running if r]
+
+
+def multi_gpu_parity(pipeline, buckets, side, dev, rank, world):
+    """Outside the timed region: one round on FRESH per-rank gradients, our bucket path against the
+    reference composition on the same inputs and the same GPUs -- torch.cat -> dist.all_reduce (NCCL,
+    in the bucket dtype) -> /= world (apex/parallel/distributed.py:11-23).  north_star: rtol 1e-3 for
+    fp16 sums.  Also: identical bits on every rank, the overflow word clean, then raised on every
+    rank by a 40000 + 40000 fp16 sum in one rank-slice.  Returns a dict with "pass"."""
+    import torch.distributed as dist
+    cur = torch.cuda.current_stream()
+    gen = torch.Generator(device=dev).manual_seed(4242 + rank)
+    out = {"buckets": len(buckets), "reference": "torch.cat -> NCCL all_reduce (fp16) -> /= world, same inputs",
+           "rtol": 1e-3}
+
+    def one_round():
+        pipeline.begin_round()
+        side.wait_stream(cur)
+        with torch.cuda.stream(side):
+            for k, b in enumerate(buckets):
+                pipeline.submit(k, [p.grad for p in b], verify=True, owners=b)
+        pipeline.join(cur)
+        torch.cuda.synchronize()
+
+    refs, absmax = [], 0.0
+    for b in buckets:
+        for p in b:
+            p.grad.copy_((torch.randn(p.shape, generator=gen, device=dev) * 65.536).to(p.grad.dtype))
+        flat = torch.cat([p.grad.reshape(-1) for p in b])
+        absmax = max(absmax, float(flat.abs().max()))
+        dist.all_reduce(flat)
+        flat /= world
+        refs.append(flat)
+    one_round()
+    amax = torch.tensor([absmax], device=dev)
+    dist.all_reduce(amax, op=dist.ReduceOp.MAX)
+    atol = 1e-3 * float(amax.item())                 # 1e-3 of the largest addend: sums near zero have no relative scale
+    close, equal, total, worst = True, 0, 0, 0.0
+    sums = []
+    for b, ref in zip(buckets, refs):
+        mine = torch.cat([p.grad.reshape(-1) for p in b])
+        close &= bool(torch.allclose(mine.float(), ref.float(), rtol=1e-3, atol=atol))
+        worst = max(worst, float((mine.float() - ref.float()).abs().max()))
+        equal += int((mine == ref).sum())
+        total += mine.numel()
+        bits = mine.view(torch.int16 if mine.dtype == torch.float16 else torch.int32).to(torch.int64)
+        sums.append(bits.sum() + (bits * (torch.arange(bits.numel(), device=dev) % 8191)).sum())
+    del refs
+    digest = torch.stack(sums)
+    every = [torch.empty_like(digest) for _ in range(world)]
+    dist.all_gather(every, digest)
+    out["averaged_grads_within_rtol"] = close
+    out["atol"] = atol
+    out["max_abs_diff"] = worst
+    out["fraction_bit_equal_to_reference"] = equal / max(total, 1)
+    out["identical_bits_on_all_ranks"] = all(bool(torch.equal(e, every[0])) for e in every)
+    out["flag_clean"] = int(pipeline.check_flag.item()) == 0
+    # a sum that overflows fp16, sitting in ONE rank's slice of the last bucket
+    victim = buckets[-1][-1].grad.view(-1)
+    victim[-8:] = 40000.0
+    one_round()
+    word = torch.tensor([int(pipeline.check_flag.item() != 0)], device=dev)
+    dist.all_reduce(word, op=dist.ReduceOp.MIN)
+    out["overflow_word_raised_on_all_ranks"] = bool(word.item()) and bool(torch.isinf(victim[-8:]).all())
+    victim[-8:] = 0.0
+    out["pass"] = all(out[k] for k in ("averaged_grads_within_rtol", "identical_bits_on_all_ranks", "flag_clean",
+                                       "overflow_word_raised_on_all_ranks"))
+    return out
+
+
 _json_out = None
 
 
@@ -393,12 +477,16 @@ def main():
     pipeline = _BucketPipeline(side)
     buckets = []
     if world > 1:
+        # what DistributedDataParallel does once it has learned the structure: one flat home per
+        # bucket (all in ONE symmetric allocation), and -- in the first round below -- every gradient
+        # becomes a view of its bucket, so later rounds have nothing to gather or scatter
         bucket_elems = int(args.bucket_mb * (1 << 20) / 2)
-        buckets = [[grads[i] for i in b] for b in build_buckets(params, bucket_elems)]
+        buckets = [[params[i] for i in b] for b in build_buckets(params, bucket_elems)]
+        pipeline.plan([(k, [p.data for p in b]) for k, b in enumerate(buckets)])
     comm_events = []
 
     def reduce_buckets():
-        """The per-bucket data path of DistributedDataParallel.comm_ready_buckets (side streams),
+        """The per-bucket data path of DistributedDataParallel.comm_ready_buckets (side stream),
         then the join of its end-of-backward epilogue."""
         cur = torch.cuda.current_stream()
         e0 = torch.cuda.Event(enable_timing=True)
@@ -407,8 +495,8 @@ def main():
         pipeline.begin_round()                       # DistributedDataParallel.forward does this
         side.wait_stream(cur)
         with torch.cuda.stream(side):
-            for k, b in enumerate(buckets):
-                pipeline.submit(k, b, verify=True)   # as comm_ready_buckets submits them
+            for k, b in enumerate(buckets):          # as comm_ready_buckets submits them
+                pipeline.submit(k, [p.grad for p in b], verify=True, owners=b)
         pipeline.join(cur)
         e1.record()
         comm_events.append((e0, e1))
@@ -428,13 +516,14 @@ def main():
             dist.barrier()
         torch.cuda.synchronize()
 
-    t_check = Timed(_C, "mt_check_overflow")
+    t_check = Timed(_C, "mt_check_overflow_publish")
     t_fused = Timed(_C, FUSED_WRAPPER[kind])
     t_ar = Timed(_C, "symm_allreduce")
 
     for _ in range(args.warmup):
         step()
     barrier()
+    del grads                                         # (N > 1: the gradients live in the buckets now)
     assert opt.overflow is False, "synthetic gradients must not overflow in the timed region"
 
     sampler = ClockSampler(local_rank)
@@ -487,9 +576,9 @@ def main():
     # ---- end to end through the public API, gradients arriving from pinned HOST memory ----------
     e2e = None
     if not args.no_e2e:
-        host = [torch.empty(g.shape, dtype=g.dtype).pin_memory() for g in grads]
-        for h, g in zip(host, grads):
-            h.copy_(g)
+        host = [torch.empty(p.grad.shape, dtype=p.grad.dtype).pin_memory() for p in params]
+        for h, p in zip(host, params):
+            h.copy_(p.grad)
         h2d = sum(h.numel() * h.element_size() for h in host)
 
         def e2e_step():
@@ -519,6 +608,14 @@ def main():
                "api": "param.grad.copy_(pinned host) ; FP16_Optimizer.update_master_grads() ; .step() ; .overflow"}
         del host
 
+    parity = None
+    if world > 1:
+        members = build_buckets(params, bucket_elems)
+        parity = multi_gpu_parity(pipeline, buckets, side, dev, rank, world)
+        parity["bucket_layout_equals_reference_rule"] = members == reference_bucket_rule(
+            [p.numel() for p in params], [p.dtype for p in params], bucket_elems)
+        parity["pass"] = parity["pass"] and parity["bucket_layout_equals_reference_rule"]
+
     gpu_ref = None
     if world == 1 and not args.no_gpu_reference:
         try:
@@ -544,7 +641,7 @@ def main():
                        "bucket_mb": args.bucket_mb if world > 1 else None, "buckets": len(buckets),
                        "l2": "no flush: %.1f GB touched per step vs 126 MB L2" % ((bpp + 2) * n_params / 1e9)},
             "roofline": roofline, "cpu_baseline": cpu, "reference_composition_on_gpu": gpu_ref, "e2e": e2e,
-            "gpu_launches": launches, "clocks": clocks,
+            "gpu_launches": launches, "clocks": clocks, "parity": parity,
             "breakdown_ms": {"check_overflow": check_ms, "fused_update": fused_ms, "bucket_allreduce_path": comm_ms,
                              "host_python_per_step": host_ms_per_step},
             "hbm_gbs_step": (bpp + 2) * n_params / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
@@ -560,22 +657,27 @@ def main():
                 kernel = {"ms_per_step": k_ms, "launches_per_step": t_ar.count() / args.steps, "algbw_gbs": k_alg,
                           "busbw_gbs": k_alg * 2 * (world - 1) / world,
                           "frac_of_900": k_alg * 2 * (world - 1) / world / 900.0,
-                          "what": "sum of the durations of the apex_b200_symm_allreduce launches (CUDA events on "
-                                  "their streams).  Consecutive buckets run on two alternating streams, so two "
-                                  "of these kernels (and the gather/scatter of their neighbours) share NVLink and "
-                                  "HBM at a time: the sum can exceed the wall time of the bucket path.  Isolated "
-                                  "kernel rate: tools/allreduce_bench.py (839 GB/s busbw at 1 GiB on 8 GPUs)"}
+                          "what": "sum of the durations of the apex_b200_symm_allreduce launches of one step (CUDA "
+                                  "events on the side stream they run on, back to back); each launch includes its "
+                                  "two in-kernel cross-rank barriers, i.e. also the time it waits for the slowest rank"}
             line["allreduce"] = {"bytes": s_bytes, "ms": comm_ms, "algbw_gbs": algbw,
-                                 "transport": "apex_b200 symmetric-memory two-shot (NVSwitch multimem beyond 2 "
-                                              "ranks, peer-to-peer at 2)" if _symm.enabled() else "NCCL",
+                                 "transport": "apex_b200 symmetric-memory two-shot, one kernel per bucket: barrier, sum "
+                                              "(NVSwitch multimem beyond 2 ranks, peer-to-peer at 2), x 1/N, inf/NaN "
+                                              "check, barrier" if _symm.enabled() else "NCCL",
                                  "kernel": kernel,
                                  "busbw_gbs": algbw * 2 * (world - 1) / world, "nvlink_peak_gbs_per_dir": 900.0,
                                  "frac_of_900": algbw * 2 * (world - 1) / world / 900.0,
-                                 "includes": "whole bucket path: gather + allreduce + x(1/N) scatter per bucket, the "
-                                             "three stages of consecutive buckets overlapped on side streams"}
+                                 "includes": "whole bucket path from the end of backward to averaged, checked gradients. "
+                                             "The gradients live in the buckets (param.grad are views of the flat "
+                                             "symmetric buffers, as DistributedDataParallel arranges after its first "
+                                             "overlapped backward), so there is no gather and no scatter; x 1/N and "
+                                             "the overflow check ride in the allreduce kernel"}
         emit(line)
     if world > 1:
         dist.destroy_process_group()
+    if parity is not None and not parity["pass"]:
+        sys.stderr.write("bench.py: multi-GPU parity FAILED: %r\n" % (parity,))
+        return 3
     return 0
 
 

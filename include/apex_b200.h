@@ -17,6 +17,9 @@
  *  - the library owns no device memory (tensors, tables and the overflow flag
  *    are allocated by the caller -- torch in practice) and keeps no mutable
  *    global state, so calls from several host threads / streams are fine.
+ *    The one exception is apex_b200_mt_l2norm_noalloc (below): it owns a fixed
+ *    256 KiB device array per GPU, caches that array's address on the host, and
+ *    calls to it that overlap on one GPU race.
  *  - there is no CPU implementation behind any of these symbols.
  *
  * The multi-tensor table
@@ -110,6 +113,20 @@ int apex_b200_flag_clear(int32_t* d_flag, void* stream);
  * ends as the FIRST bad tensor.  No host sync.  The flag is not cleared here. */
 int apex_b200_mt_check_overflow(const apex_b200_mt_table* t, int grad_list,
                                 int32_t* d_flag, void* stream);
+
+/* The same scan (apex/fp16_utils/loss_scaler.py:84-110 under fp16_optimizer.py:213-221) for a caller
+ * that wants nothing else on the stream between the check and the update it predicates
+ * (fp16_optimizer.py:493-497 then :372-380): the last CTA to finish
+ *   - stores the final word to *h_mirror, a word of PINNED (mapped) host memory, if not NULL -- the
+ *     host reads it after an event recorded behind this launch, no device-to-host copy needed;
+ *   - sets *d_rearm = 0 if not NULL: with two words used alternately, each check clears the word of
+ *     the next one and no cudaMemset is ever enqueued (d_rearm must differ from d_flag).
+ * d_ticket: one int32 of device memory, zero before the first call, owned by this sequence of calls
+ * (the kernel leaves it zero); required when h_mirror or d_rearm is given.  *d_flag must be zero
+ * (or hold an earlier check's verdict to be merged) on entry, as for apex_b200_mt_check_overflow. */
+int apex_b200_mt_check_overflow_publish(const apex_b200_mt_table* t, int grad_list, int32_t* d_flag,
+                                        int32_t* d_ticket, int32_t* h_mirror, int32_t* d_rearm,
+                                        void* stream);
 
 /* In-place fp32 `g *= inv_scale`.
  * mode 0 replaces FP16_Optimizer._downscale_master
@@ -232,21 +249,51 @@ int apex_b200_mt_scale_unflatten(const apex_b200_mt_table* t, const void* flat,
 int apex_b200_scale_flat(void* flat, int64_t numel, int dtype, double divisor,
                          int32_t* d_flag, void* stream);
 
-/* Replaces `dist.all_reduce(coalesced)` of apply_flat_dist_call
- * (apex/parallel/distributed.py:15-17) for a flat bucket that lives in peer-mapped
- * ("symmetric") memory of one NVLink domain: in-place SUM over `world` GPUs, two-shot,
- * rank r reducing slice r and writing it to every copy.  With `multicast_ptr != 0`
- * the NVSwitch does both halves (multimem.ld_reduce / multimem.st); otherwise
- * `peer_ptrs[world]` (host array of the buffer's address on every rank, own rank
- * included) is used with plain loads/stores over NVLink.  fp16 (dtype 0) is summed in
- * fp32 and rounded once; fp32 is dtype 1.  numel must be a multiple of
- * (16 / element size) * world (pad the buffer).  The call only launches this rank's
- * kernel; the caller must order it after every rank has filled its buffer and must
- * not read the result before every rank's kernel has finished (a cross-rank barrier
- * on the stream before and after).  ctas <= 0 picks a default. */
-int apex_b200_symm_allreduce(const uint64_t* peer_ptrs, uint64_t multicast_ptr,
-                             int rank, int world, int64_t numel, int dtype,
-                             int ctas, void* stream);
+/* ---- bucket averaging over symmetric memory ------------------------------- */
+
+/* One symmetric (peer-mapped) allocation of an NVLink domain, as seen from this rank.  The caller
+ * allocates it (torch.distributed._symmetric_memory here: plumbing), zero-fills it once, and exchanges
+ * the addresses; the library only computes with them.  Inside the allocation the caller reserves
+ * APEX_B200_SYMM_SIGNAL_BYTES for the cross-rank signal words ([channel][cta][rank] uint32, zero at
+ * the start, never reset) and, optionally, 4-byte overflow words. */
+#define APEX_B200_SYMM_MAX_WORLD 16
+#define APEX_B200_SYMM_MAX_CTAS 256
+#define APEX_B200_SYMM_CHANNELS 2
+#define APEX_B200_SYMM_SIGNAL_BYTES (APEX_B200_SYMM_CHANNELS * APEX_B200_SYMM_MAX_CTAS * APEX_B200_SYMM_MAX_WORLD * 4)
+
+typedef struct apex_b200_symm_domain {
+    int32_t rank, world;
+    uint64_t peer_base[APEX_B200_SYMM_MAX_WORLD]; /* address of the allocation on every rank, own included */
+    uint64_t multicast_base;                      /* NVSwitch multicast alias of the allocation, or 0    */
+    uint64_t signal_offset;                       /* byte offset of the signal words (16 B aligned)      */
+    uint64_t timeout_ns;                          /* a rank that waits longer for a peer traps; 0 = never */
+} apex_b200_symm_domain;
+
+/* Replaces `dist.all_reduce(coalesced)` AND `coalesced /= dist.get_world_size()` of
+ * apply_flat_dist_call (apex/parallel/distributed.py:15-20) for a flat bucket at byte `offset` of the
+ * symmetric allocation, in ONE kernel per rank, and performs on the way the inf/NaN test that
+ * FP16_Optimizer._check_overflow (apex/fp16_utils/fp16_optimizer.py:213-221) would run over the
+ * averaged gradients: in-place two-shot SUM over `world` GPUs (rank r reduces slice r and writes it
+ * to every copy), result = T(opmath(sum) * (opmath)(1.0 / divisor)) when apply_mul != 0 (torch's CUDA
+ * true-divide by a python scalar), fp16 (dtype 0) summed in fp32 and rounded once to fp16 before the
+ * multiply, fp32 is dtype 1.  With flag_offset >= 0 the 4-byte word at that offset of EVERY rank's
+ * allocation is raised to INT32_MAX when any averaged value is inf/NaN (the kernel sees the flat
+ * bucket, not tensors, so the word carries no tensor index); clear it with apex_b200_flag_clear on a
+ * stream ordered before the launch.
+ *
+ * The cross-rank ordering is inside the kernel: it starts by waiting until the kernel of the same
+ * `seq` has started on every rank (so each rank's bucket is final: order the launch after whatever
+ * fills the bucket) and it exits only after every rank has written its slice everywhere (so whatever
+ * follows in stream order may read the whole bucket).  Every rank must call with the same offset,
+ * numel, channel, seq, use_multicast and ctas; `seq` starts at 1 and grows by 1 per call on a
+ * (allocation, channel); calls on one channel must not overlap on the GPU (one stream per channel).
+ * use_multicast != 0 lets the NVSwitch do both halves (multimem.ld_reduce / multimem.st, needs
+ * multicast_base); otherwise plain loads/stores over NVLink.  numel must be a multiple of
+ * (16 / element size) * world (pad the bucket with zeros).  ctas <= 0 picks a default.
+ * One process per GPU: the kernel spins on words written by OTHER GPUs. */
+int apex_b200_symm_allreduce(const apex_b200_symm_domain* d, uint64_t offset, int64_t numel,
+                             int dtype, double divisor, int apply_mul, int64_t flag_offset,
+                             int channel, uint32_t seq, int use_multicast, int ctas, void* stream);
 
 /* ---- gradient norm (clip_master_grads) ---------------------------------- */
 

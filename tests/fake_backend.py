@@ -13,6 +13,7 @@ import numpy as np
 import torch
 
 from apex_b200 import _C
+from apex_b200.multi_tensor import TensorTable
 from oracle import c_oracle
 
 INT32_MAX = 0x7FFFFFFF
@@ -46,6 +47,14 @@ def mt_check_overflow(table, grad_list, flag, stream=None):
             flag[0] = max(int(flag[0]), INT32_MAX - i)
             # keep scanning: the word must end as the FIRST bad tensor = the max value
     # (max over all bad tensors of INT32_MAX - i is reached at the smallest i)
+
+
+def mt_check_overflow_publish(table, grad_list, flag, ticket, host_mirror, rearm, stream=None):
+    mt_check_overflow(table, grad_list, flag)
+    if host_mirror is not None:
+        host_mirror[0] = int(flag[0])
+    if rearm is not None:
+        rearm.zero_()
 
 
 def mt_unscale(table, grad_list, inv_scale, flag, mode, stream=None):
@@ -208,6 +217,17 @@ def mt_clip_by_norm(table, grad_list, norm, max_norm, flag, stream=None):
         _flat(g)[:] = _flat(g) * coef
 
 
+_real_update = TensorTable.update
+
+
+def _recording_update(self, lists, flags=None):
+    """TensorTable.update that also keeps the tensors themselves, so that the doubles above can walk
+    them (the real table only holds addresses)."""
+    self.lists = [list(l) for l in lists]
+    self.flags = np.zeros(len(lists[0]), dtype=np.int32) if flags is None else np.asarray(flags, dtype=np.int32)
+    return _real_update(self, lists, flags)
+
+
 class _Event(object):
     def record(self, *a, **k):
         pass
@@ -237,8 +257,8 @@ def _cuda_named_type(self, *a, **k):
 def install(monkeypatch):
     """Swap the kernel wrappers for the doubles and make torch.cuda plumbing inert."""
     del calls[:]
-    monkeypatch.setattr(_C, "keep_table_refs", True, raising=False)
-    for name in ("flag_clear", "mt_check_overflow", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
+    monkeypatch.setattr(TensorTable, "update", _recording_update)
+    for name in ("flag_clear", "mt_check_overflow", "mt_check_overflow_publish", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
                  "mt_copy", "mt_zero", "mt_fused_sgd", "mt_fused_adam", "mt_flatten", "mt_scale_unflatten",
                  "scale_flat", "mt_l2norm", "mt_clip_by_norm", "mt_larc"):
         monkeypatch.setattr(_C, name, globals()[name])

@@ -208,3 +208,35 @@ def test_table_identity_fast_path_is_voided_when_a_tensor_dies():
     assert t.built_from([a, d])
     t.invalidate()
     assert not t.built_from([a, d])
+
+
+def test_symm_allreduce_validates_before_any_cuda_call():
+    """apex_b200_symm_allreduce: arguments that cannot describe a collective are refused on the host."""
+    import ctypes
+    lib = _C.lib
+    d = _C.SymmDomain()
+    d.rank, d.world = 0, 2
+    d.peer_base[0], d.peer_base[1] = 1 << 20, 2 << 20
+
+    def call(dom, offset=0, numel=32, dtype=0, divisor=2.0, apply_mul=1, flag_off=-1, channel=0, seq=1, mc=0, ctas=0):
+        return lib.apex_b200_symm_allreduce(ctypes.byref(dom) if dom is not None else None, offset, numel, dtype,
+                                            divisor, apply_mul, flag_off, channel, seq, mc, ctas, None)
+    assert call(None) == -1
+    assert call(d, numel=24) == -1                      # not a multiple of 8 halfs x 2 ranks
+    assert call(d, offset=8) == -1                      # bucket not 16 B aligned
+    assert call(d, dtype=2) == -1                       # fp64 is not supported
+    assert call(d, seq=0) == -1                         # seq starts at 1
+    assert call(d, channel=_C.SYMM_CHANNELS) == -1
+    assert call(d, divisor=0.0) == -1
+    assert call(d, mc=1) == -1                          # no multicast alias in this domain
+    assert call(d, flag_off=6) == -1
+    assert call(d, ctas=_C.SYMM_MAX_CTAS + 1) == -2     # APEX_B200_ERANGE
+    assert call(d, numel=0) == 0                        # nothing to do
+    bad = _C.SymmDomain()
+    bad.rank, bad.world = 2, 2
+    assert call(bad) == -1
+    # the python-side constants mirror the header
+    header = open(HEADER).read()
+    assert "#define APEX_B200_SYMM_MAX_WORLD %d" % _C.SYMM_MAX_WORLD in header
+    assert "#define APEX_B200_SYMM_MAX_CTAS %d" % _C.SYMM_MAX_CTAS in header
+    assert "#define APEX_B200_SYMM_CHANNELS %d" % _C.SYMM_CHANNELS in header

@@ -100,6 +100,63 @@ def test_delay_allreduce_and_refresh_on_param_change(gloo_single):
     assert sum(ddp2.bucket_sizes) == 5
 
 
+def test_gradients_move_into_their_buckets(gloo_single):
+    """After the first overlapped backward every param.grad is a view of its bucket's flat home
+    (SURVEY 8f N2): later iterations neither gather nor scatter, autograd accumulates in place; a
+    gradient the user dropped (set_to_none) is copied in once and becomes a view again."""
+    from apex_b200.parallel import DistributedDataParallel as DDP
+    from apex_b200.parallel.distributed import verified_flag
+    calls = gloo_single.calls
+    torch.manual_seed(1)
+    net = build_layout_model("mlp3")
+    ref = build_layout_model("mlp3")
+    ref.load_state_dict(net.state_dict())
+    ddp = DDP(net, message_size=50)
+
+    def run(x, set_to_none):
+        net.zero_grad(set_to_none=set_to_none)
+        ref.zero_grad(set_to_none=True)
+        del calls[:]
+        ddp(x).pow(2).sum().backward()
+        ref(x).pow(2).sum().backward()
+        for p, q in zip(net.parameters(), ref.parameters()):
+            assert torch.equal(p.grad, q.grad)                       # world 1: x (1/1) is exact
+
+    def homes():
+        out = []
+        for b, params in enumerate(ddp._bucket_params):
+            home = ddp._pipeline.slots[b][0]
+            for p, v in zip(params, home.views):
+                out.append(p.grad is v)
+                lo = home.flat.data_ptr()
+                assert lo <= v.data_ptr() < lo + home.flat.numel() * home.flat.element_size()
+                assert v.data_ptr() % 32 == 0
+        return out
+
+    x = torch.randn(5, 6)
+    run(x, True)                                                     # learns the structure (flat call)
+    assert "flatten" in calls and ddp.num_buckets == 3
+    run(x, True)                                                     # first overlapped: strays are re-homed
+    assert calls.count("copy") == 3 and "flatten" not in calls and "scale_unflatten" not in calls
+    assert all(homes())
+    run(x, False)                                                    # zeroed in place: nothing to move
+    assert "copy" not in calls and "flatten" not in calls and calls.count("scale_flat") == 3
+    assert all(homes())
+    assert verified_flag([p.grad for p in net.parameters()]) is ddp._pipeline.check_flag
+    run(x, True)                                                     # dropped gradients come back as views
+    assert calls.count("copy") == 3 and all(homes())
+    # one gradient replaced by hand: only that bucket copies
+    first = next(net.parameters())
+    net.zero_grad(set_to_none=False)
+    first.grad = torch.zeros_like(first)
+    ref.zero_grad(set_to_none=True)
+    del calls[:]
+    ddp(x).pow(2).sum().backward()
+    ref(x).pow(2).sum().backward()
+    assert calls.count("copy") == 1 and all(homes())
+    assert all(torch.equal(p.grad, q.grad) for p, q in zip(net.parameters(), ref.parameters()))
+
+
 # ---- world size 2 -------------------------------------------------------------------------------
 
 def _install_double():
@@ -107,8 +164,9 @@ def _install_double():
     import contextlib as _ctx
     from apex_b200 import _C
     from tests import fake_backend as fb
-    _C.keep_table_refs = True
-    for name in ("flag_clear", "mt_check_overflow", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
+    from apex_b200.multi_tensor import TensorTable
+    TensorTable.update = fb._recording_update
+    for name in ("flag_clear", "mt_check_overflow", "mt_check_overflow_publish", "mt_unscale", "mt_grads_to_master", "mt_master_to_model",
                  "mt_copy", "mt_zero", "mt_fused_sgd", "mt_fused_adam", "mt_flatten", "mt_scale_unflatten",
                  "scale_flat", "mt_l2norm", "mt_clip_by_norm", "mt_larc"):
         setattr(_C, name, getattr(fb, name))

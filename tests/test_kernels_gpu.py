@@ -78,6 +78,41 @@ def test_check_overflow_clean_and_first_bad(chunk):
     assert int(f.item()) == INT32_MAX - 9
 
 
+@pytest.mark.parametrize("chunk", [2048, 65536])
+def test_check_overflow_publish_mirrors_to_pinned_host_and_rearms(chunk):
+    """The check whose last CTA publishes the verdict to pinned host memory and zeroes the NEXT word:
+    same verdicts as apex_b200_mt_check_overflow, no memset and no device-to-host copy needed."""
+    grads, flags = _mixed_grads(3)
+    t = table([grads], flags, chunk)
+    words = torch.zeros(4, dtype=torch.int32, device=dev())
+    pair, ticket = (words[0:1], words[1:2]), words[2:3]
+    host = torch.full((1,), -7, dtype=torch.int32).pin_memory()
+    plain = flag()
+    turn = 0
+    for it, bad in enumerate([None, 5, None, 0, 11, 11, None]):
+        saved = None
+        if bad is not None:
+            saved = grads[bad][grads[bad].numel() // 2].clone()
+            grads[bad][grads[bad].numel() // 2] = float("nan") if it % 2 else float("inf")
+        turn ^= 1
+        _C.mt_check_overflow_publish(t, 0, pair[turn], ticket, host, pair[turn ^ 1])
+        _C.flag_clear(plain)
+        _C.mt_check_overflow(t, 0, plain)
+        torch.cuda.synchronize()
+        want = 0 if bad is None else INT32_MAX - bad
+        assert int(plain.item()) == want
+        assert int(pair[turn].item()) == want and int(host[0]) == want, (it, bad)
+        assert int(pair[turn ^ 1].item()) == 0 and int(ticket.item()) == 0
+        if bad is not None:
+            grads[bad][grads[bad].numel() // 2] = saved
+    # nothing to scan: the mirror and the re-armed word are still produced
+    empty = table([[]])
+    pair[0].fill_(9)
+    _C.mt_check_overflow_publish(empty, 0, pair[1], ticket, host, pair[0])
+    torch.cuda.synchronize()
+    assert int(pair[0].item()) == 0 and int(ticket.item()) == 0
+
+
 def test_check_overflow_empty_inputs():
     f = flag()
     t = table([[]])
