@@ -158,7 +158,13 @@ def device_info():
     return sm.value, ma.value, mi.value
 
 
+_raw_stream = getattr(torch._C, "_cuda_getCurrentRawStream", None)
+
+
 def current_stream():
+    """cudaStream_t of torch's current stream on the current device, as an int."""
+    if _raw_stream is not None:
+        return _raw_stream(torch.cuda.current_device())
     return torch.cuda.current_stream().cuda_stream
 
 

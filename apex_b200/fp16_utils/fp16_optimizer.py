@@ -29,6 +29,7 @@ subclass whose ``grad`` property does that -- and from there on the code follows
 the reference's unfused sequence on multi-tensor kernels.  DESIGN.md lists the
 (few, deliberate) observable differences.
 """
+import operator
 import weakref
 
 import torch
@@ -105,6 +106,7 @@ class _StepPlan(object):
         self.state_map = None
         self.state_len = 0
         self.state_dicts = None
+        self._held_columns = ()
         self._watch = ()
         self._watch_ptrs = ()
         self._cursor = 0
@@ -226,6 +228,7 @@ class _StepPlan(object):
         self.state_map = state
         self.state_len = len(state)
         self.state_dicts = [state[p] for p in self.owners] if self.state_keys else []
+        self._held_columns = [[held[k] for held in self.state_tensors] for k in range(len(self.state_keys))]
 
     def still_valid(self, kind, from_masters, group, grads, state):
         if kind != self.kind or from_masters != self.from_masters or self.fresh:
@@ -240,17 +243,14 @@ class _StepPlan(object):
         # per-parameter dicts we saw at build time must still hold the very same tensors
         if state is not self.state_map or len(state) != self.state_len:
             return False
-        keys = self.state_keys
-        if len(keys) == 1:
-            key = keys[0]
-            for st, held in zip(self.state_dicts, self.state_tensors):
-                if st.get(key) is not held[0]:
-                    return False
-        elif keys:
-            for st, held in zip(self.state_dicts, self.state_tensors):
-                for key, t in zip(keys, held):
-                    if st.get(key) is not t:
-                        return False
+        for k, key in enumerate(self.state_keys):
+            held = self._held_columns[k]
+            try:
+                now = list(map(operator.itemgetter(key), self.state_dicts))
+            except KeyError:
+                return False
+            if not all(map(operator.is_, now, held)):
+                return False
         if self.steps is not None:
             if self.state_dicts[0].get('step') is not self.steps[0] or \
                     self.state_dicts[-1].get('step') is not self.steps[-1]:
@@ -336,6 +336,17 @@ class FP16_Optimizer(object):
             self.fp32_from_fp16_groups.append(masters)
             self.fp32_from_fp32_groups.append(floats)
 
+        # flat views of the three list-of-lists, for the per-step walks (one comprehension each)
+        self._flat_halves = [p for g in self.fp16_groups for p in g]
+        self._flat_floats = [p for g in self.fp32_from_fp32_groups for p in g]
+        self._spans = []
+        a = b = 0
+        for halves, floats in zip(self.fp16_groups, self.fp32_from_fp32_groups):
+            self._spans.append((a, a + len(halves), b, b + len(floats)))
+            a += len(halves)
+            b += len(floats)
+        self._g16 = self._g32 = None      # this iteration's gradients, read once in update_master_grads
+
         # recast pre-existing per-param state to the masters' dtype (reference :158)
         self.optimizer.load_state_dict(self.optimizer.state_dict())
 
@@ -353,6 +364,14 @@ class FP16_Optimizer(object):
         self._overflow_event = None      # set while the device word has not been read yet
         self.first_closure_call_this_step = True
         self.clip_grad_norm = clip_grad_norm
+        # clip_master_grads with the 2-norm: True = norm straight from the fp16 gradients and the
+        # factor applied inside the fused update (a TOLERANCE path: the norm is summed in another order
+        # than torch's, so the factor may differ in its last bits); False = materialise the master
+        # gradients and call torch's clip_grad_norm_ as the reference does (bit-exact, ~3x the traffic)
+        self.fused_clip = True
+        # how many step() calls went through the wrapped optimizer's own step() + a copy-back launch
+        # because no fused kernel applies (inner optimizer other than SGD/Adam/AdamW, amsgrad, ...)
+        self.unfused_steps = 0
 
         # device-side plumbing (created on first use)
         self._device = None
@@ -421,6 +440,7 @@ class FP16_Optimizer(object):
         self._pending = None
         self._grads_ready = False
         self._clip = None
+        self._g16 = self._g32 = None
         if set_grads_to_None:
             for group in self.optimizer.param_groups:
                 for p in group['params']:
@@ -472,17 +492,8 @@ class FP16_Optimizer(object):
                      [p for g in self.fp32_from_fp32_groups for p in g]
             self.overflow = self.loss_scaler.has_overflow(params)
             return
-        grads = []
-        for group in self.fp16_groups:
-            for param in group:
-                g = param.grad
-                if g is not None:
-                    grads.append(g)
-        for group in self.fp32_from_fp32_groups:
-            for param in group:
-                g = param.grad
-                if g is not None:
-                    grads.append(g)
+        # fp16 gradients, then the fp32-native ones (the reference's order, :214-220)
+        grads = [g for g in self._g16 + self._g32 if g is not None]
         if not grads:
             self.overflow = False
             return
@@ -611,7 +622,7 @@ class FP16_Optimizer(object):
         """
         if self.overflow:
             return -1
-        if self._pending is not None and self._clip is None and norm_type in (2, 2.0) \
+        if self.fused_clip and self._pending is not None and self._clip is None and norm_type in (2, 2.0) \
                 and self.clip_grad_norm is clip_grad_norm and self._groups_intact():
             return self._clip_virtual(max_norm)
         fp32_params = []
@@ -623,9 +634,12 @@ class FP16_Optimizer(object):
     def _groups_intact(self):
         """The inner optimizer's param groups still hold exactly the parameters seen at construction."""
         groups = self.optimizer.param_groups
-        return len(groups) == len(self.fp16_groups) and all(
-            len(g['params']) == len(h) + len(f)
-            for g, h, f in zip(groups, self.fp16_groups, self.fp32_from_fp32_groups))
+        if len(groups) != len(self.fp16_groups) or len(groups) != len(self._spans):
+            return False
+        for g, h, f, (a, b, c, d) in zip(groups, self.fp16_groups, self.fp32_from_fp32_groups, self._spans):
+            if len(g['params']) != len(h) + len(f) or b - a != len(h) or d - c != len(f):
+                return False
+        return True
 
     def _clip_virtual(self, max_norm):
         inv_scale, apply_scale = self._pending
@@ -727,6 +741,13 @@ class FP16_Optimizer(object):
             commit()
             retval = None
         else:
+            if self.unfused_steps == 0:
+                import warnings
+                warnings.warn("apex_b200: FP16_Optimizer.step() is not taking the fused update for %s "
+                              "(no fused kernel for this optimizer or these options); using the wrapped "
+                              "optimizer's own step() plus one copy-back launch.  Counted in .unfused_steps."
+                              % type(self.optimizer).__name__)
+            self.unfused_steps += 1
             retval = self.optimizer.step()
             self._master_params_to_model_params()
 
@@ -829,11 +850,13 @@ class FP16_Optimizer(object):
         halves = self.fp16_groups[gi]
         masters = self.fp32_from_fp16_groups[gi]
         floats = self.fp32_from_fp32_groups[gi]
+        a, b, c, d = self._spans[gi]
         if from_masters:
-            grads = [_raw_grad(m) for m in masters]
+            grads = [_raw_grad(m) for m in masters] + [p.grad for p in floats]
+        elif self._g16 is not None and len(self._g16) == len(self._flat_halves):
+            grads = self._g16[a:b] + self._g32[c:d]
         else:
-            grads = [h.grad for h in halves]
-        grads += [p.grad for p in floats]
+            grads = [h.grad for h in halves] + [p.grad for p in floats]
         if not grads:
             return None
         plan = self._plans.get(gi)
@@ -861,6 +884,15 @@ class FP16_Optimizer(object):
         self._pending = None
         self._grads_ready = False
         self._clip = None
+        # every param.grad is read ONCE per iteration; the check, the in-place unscale and the launch
+        # plan of step() all work on these lists (a gradient replaced between here and step() is not
+        # seen, as in the reference, whose master gradients are a snapshot taken here)
+        if self._groups_intact():
+            self._g16 = [p.grad for p in self._flat_halves]
+            self._g32 = [p.grad for p in self._flat_floats]
+        else:
+            self._g16 = [p.grad for g in self.fp16_groups for p in g]
+            self._g32 = [p.grad for g in self.fp32_from_fp32_groups for p in g]
         if self.dynamic_loss_scale:
             self._check_overflow()
             # reference: `if self.overflow: return`.  The decision is still on the
@@ -875,7 +907,7 @@ class FP16_Optimizer(object):
         if apply_scale:
             groups = self.optimizer.param_groups
             if self._groups_intact():
-                grads = [p.grad for g in self.fp32_from_fp32_groups for p in g if p.grad is not None]
+                grads = [g for g in self._g32 if g is not None]
             else:
                 # param_groups were edited after wrapping: the reference unscales the gradient of
                 # EVERY parameter the inner optimizer owns (:236-241); masters are handled virtually

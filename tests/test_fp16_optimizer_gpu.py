@@ -94,7 +94,16 @@ def _make_pair(shapes16, shapes32, make_inner, seed, **fp16_kwargs):
     return mine, theirs, opt, ref, g
 
 
-def _same_run(mine, theirs, opt, ref, g, iters, inject, clip=None, exact=True):
+def _same_run(mine, theirs, opt, ref, g, iters, inject, clip=None, exact=True, lr=None):
+    """exact=False (fused clip_master_grads only): the clip factor comes from a norm summed in
+    another order than torch's and may differ from the reference's in its last bits (asserted below:
+    the returned norm within 4 fp32 ulp, hence the factor within ~4 ulp = 2^-21 relative).  With plain
+    SGD a relative change eps of the factor moves element i by lr * |clipped gradient i| * eps, plus one
+    rounding of the parameter: the masters must stay within the element-wise budget
+        sum over committed steps of ( lr * |g_i| * 2^-21 + ulp(p_i) ),
+    g_i being the reference's own clipped master gradient."""
+    committed = 0
+    budget = [torch.zeros_like(rm, dtype=torch.float64) for rm in ref.masters] if not exact else None
     for it in range(iters):
         scale = float(opt.loss_scale)
         assert scale == float(ref.loss_scale)
@@ -110,21 +119,36 @@ def _same_run(mine, theirs, opt, ref, g, iters, inject, clip=None, exact=True):
             ref.update_master_grads()
             if clip is not None:
                 a, b = opt.clip_master_grads(clip), ref.clip_master_grads(clip)
-                assert float(a) == pytest.approx(float(b), rel=1e-5)
+                if exact:
+                    assert float(a) == float(b)
+                else:
+                    assert abs(float(a) - float(b)) <= 4 * float(np.spacing(np.float32(abs(float(b)))))
             opt.step()
             ref.step()
+        committed += int(not opt.overflow)
+        if not exact and not ref.overflow:
+            for b, rm in zip(budget, ref.masters):
+                b += lr * rm.grad.abs().double() * 2.0**-21
+                b += torch.ldexp(torch.ones_like(b), torch.frexp(rm.data)[1] - 24)        # ulp of the fp32 value
         assert opt.overflow == ref.overflow, it
         assert float(opt.loss_scale) == float(ref.loss_scale), it
         if opt.dynamic_loss_scale:
             assert opt.loss_scaler.cur_iter == ref.scaler.cur_iter
             assert opt.loss_scaler.last_overflow_iter == ref.scaler.last_overflow_iter
+    seen_budget = []
     for m, rm in zip(opt.fp32_from_fp16_groups[0], ref.masters):
         d = ulp_diff(m.data.cpu().numpy(), rm.data.cpu().numpy())
         if exact:
             assert d.max() <= 1                          # north_star tolerance
             assert torch.equal(m.data, rm.data)          # measured: identical
         else:
-            assert torch.allclose(m.data, rm.data, rtol=1e-5, atol=1e-7)
+            diff = (m.data.double() - rm.data.double()).abs()
+            used = float((diff / budget[len(seen_budget)]).max())
+            seen_budget.append(used)
+            print("fused clip: %.3f of the element-wise error budget used after %d committed steps; "
+                  "max distance %d ulp of the parameter itself, %.4f%% of elements bit-equal"
+                  % (used, committed, int(d.max()), 100.0 * (d == 0).mean()))
+            assert used <= 1.0
     for p, q in zip(mine, theirs):
         if exact:
             assert torch.equal(p.data, q.data)
@@ -195,11 +219,36 @@ def test_config4_clip_master_grads():
     shapes = [(3331, 150), (600, 150), (600, 150), (600,), (600,), (3331,)]
     mine, theirs, opt, ref, g = _make_pair(shapes, [], lambda ps: torch.optim.SGD(ps, lr=1.0), 24,
                                            dynamic_loss_scale=True, dynamic_loss_args={"init_scale": 2**15, "scale_window": 6})
-    _same_run(mine, theirs, opt, ref, g, 12, {3: (1, 17, INF), 4: (5, 0, NAN)}, clip=0.25, exact=False)
+    _same_run(mine, theirs, opt, ref, g, 12, {3: (1, 17, INF), 4: (5, 0, NAN)}, clip=0.25, exact=False, lr=1.0)
     # overflow -> clip returns -1 without touching anything
     mine[0].grad[0, 0] = INF
     opt.update_master_grads()
     assert opt.clip_master_grads(0.25) == -1
+
+
+def test_config4_clip_master_grads_exact_path():
+    """fused_clip = False: master gradients are materialised and torch's own clip_grad_norm_ runs on
+    them, as in the reference (fp16_optimizer.py:243-265) -- bit-exact, norm included."""
+    shapes = [(3331, 150), (600, 150), (600, 150), (600,), (600,), (3331,)]
+    mine, theirs, opt, ref, g = _make_pair(shapes, [], lambda ps: torch.optim.SGD(ps, lr=20.0), 24,
+                                           dynamic_loss_scale=True, dynamic_loss_args={"init_scale": 2**15, "scale_window": 6})
+    opt.fused_clip = False
+    _same_run(mine, theirs, opt, ref, g, 12, {3: (1, 17, INF), 4: (5, 0, NAN)}, clip=0.25, exact=True)
+
+
+def test_documented_exclusion_finite_fp32_values_whose_sum_overflows():
+    """SURVEY 8a A11 / DESIGN section 3: the reference decides by float(x.float().sum()), so fp32
+    gradients [3e38, 3e38] -- finite, but their SUM is inf -- count as an overflow there (golden
+    `two_3e38_f32`: True; torch's reduction order decides such cases).  This implementation tests
+    the ELEMENTS: the same input is NOT an overflow here.  Pinned so that the documented answer
+    cannot move unnoticed.  fp16 gradients can never be in this situation (65504 * numel << 3.4e38)."""
+    from apex_b200.fp16_utils import DynamicLossScaler
+    x = torch.tensor([3e38, 3e38], device=dev())
+    assert bool(torch.isinf(x.sum()))                                   # what the reference would see
+    assert DynamicLossScaler._has_inf_or_nan(x) is False                # the documented answer here
+    assert DynamicLossScaler._has_inf_or_nan(torch.tensor([3e38, float("inf")], device=dev())) is True
+    big16 = torch.full((1000000,), 65504.0, device=dev()).half()
+    assert DynamicLossScaler._has_inf_or_nan(big16) is False            # agrees with the reference's probe
 
 
 def test_static_scale_does_no_check_and_one_launch():
@@ -379,7 +428,7 @@ def test_config4_lstm_full_shapes_with_clipping():
                                            dynamic_loss_scale=True,
                                            dynamic_loss_args={"init_scale": 2**14, "scale_window": 4})
     inject = {2: (10, V - 1, INF), 3: (0, V * H - 3, NAN), 7: (5, 12345, -INF)}
-    _same_run(mine, theirs, opt, ref, g, 10, inject, clip=0.25, exact=False)
+    _same_run(mine, theirs, opt, ref, g, 10, inject, clip=0.25, exact=False, lr=20.0)
 
 
 def test_config5_gpt2_xl_full_size_adam_properties():

@@ -685,3 +685,65 @@ def test_amp_handle_and_wrapper_against_golden_runs_of_the_reference(golden_json
         assert w2.data.tolist() == row["w"]
         assert [repr(x) for x in w2.grad.tolist()] == row["grad"]      # incl. the un-unscaled gradient of the bad loss
         assert [sc.loss_scale() for sc in wrapped._loss_scaler] == row["scales"]
+
+
+def test_unfused_steps_are_counted_and_announced_once(cpu_backend):
+    """An inner optimizer without a fused kernel goes through its own step() + one copy-back launch, as
+    the reference does with every optimizer (fp16_optimizer.py:380-382): legitimate, but not silent."""
+    import warnings
+    from apex_b200.fp16_utils import FP16_Optimizer
+    ps = [torch.nn.Parameter((torch.randn(40) * 0.1).half()), torch.nn.Parameter(torch.randn(9) * 0.1)]
+    opt = FP16_Optimizer(torch.optim.RMSprop(ps, lr=0.01), static_loss_scale=4.0, verbose=False)
+    with warnings.catch_warnings(record=True) as seen:
+        warnings.simplefilter("always")
+        for it in range(3):
+            for p in ps:
+                p.grad = torch.ones_like(p)
+            opt.update_master_grads()
+            opt.step()
+    assert opt.unfused_steps == 3
+    assert len([w for w in seen if "not taking the fused update for RMSprop" in str(w.message)]) == 1
+    assert "master_to_model" in cpu_backend.calls
+    # a fused optimizer never counts
+    qs = [torch.nn.Parameter((torch.randn(40) * 0.1).half())]
+    opt2 = FP16_Optimizer(torch.optim.SGD(qs, lr=0.01), static_loss_scale=4.0, verbose=False)
+    qs[0].grad = torch.ones_like(qs[0])
+    opt2.update_master_grads()
+    opt2.step()
+    assert opt2.unfused_steps == 0 and "fused_sgd" in cpu_backend.calls
+
+
+def test_storage_swapped_under_an_unchanged_identity_is_noticed(cpu_backend):
+    """`p.data = ...` keeps the python object and changes the address (EMA swap, module.half()): the
+    cached launch plan and tables must not keep the old addresses."""
+    from apex_b200.fp16_utils import FP16_Optimizer
+    from oracle import apex_ref
+    init = [(torch.randn(300) * 0.1).half(), (torch.randn(7, 9) * 0.1).half(), (torch.randn(50) * 0.1).half()]
+    ps = [torch.nn.Parameter(t.clone()) for t in init]
+    rs = [torch.nn.Parameter(t.clone()) for t in init]
+    make = lambda q: torch.optim.SGD(q, lr=0.5, momentum=0.9)      # noqa: E731
+    opt = FP16_Optimizer(make(ps), static_loss_scale=8.0, verbose=False)
+    ref = apex_ref.MixedPrecisionStep(rs, make, static_loss_scale=8.0)
+    for it in range(6):
+        gs = [(torch.randn(t.shape) * 8).half() for t in init]
+        if it == 3:
+            for p, r in zip(ps, rs):                          # new storage, same objects, same values
+                p.data = p.data.clone()
+                r.data = r.data.clone()
+            gs_objs = [p.grad for p in ps]
+            for g_old in gs_objs:                             # gradients too: same objects, new storage
+                g_old.data = g_old.data.clone()
+        for p, r, g in zip(ps, rs, gs):
+            if p.grad is None:
+                p.grad = g.clone()
+            else:
+                p.grad.data.copy_(g)
+            r.grad = g.clone()
+        opt.update_master_grads()
+        ref.update_master_grads()
+        opt.step()
+        ref.step()
+    for p, r in zip(ps, rs):
+        assert torch.equal(p.data, r.data)
+    for m, rm in zip(opt.fp32_from_fp16_groups[0], ref.masters):
+        assert torch.equal(m.data, rm.data)

@@ -89,7 +89,7 @@ def test_check_overflow_publish_mirrors_to_pinned_host_and_rearms(chunk):
     host = torch.full((1,), -7, dtype=torch.int32).pin_memory()
     plain = flag()
     turn = 0
-    for it, bad in enumerate([None, 5, None, 0, 11, 11, None]):
+    for it, bad in enumerate([None, 5, None, 1, 11, 11, None]):
         saved = None
         if bad is not None:
             saved = grads[bad][grads[bad].numel() // 2].clone()
