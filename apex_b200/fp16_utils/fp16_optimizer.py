@@ -76,6 +76,19 @@ class _MasterParam(torch.Tensor):
         return plain.__reduce_ex__(proto)
 
 
+# torch.optim picks its multi-tensor ("foreach") implementation only for tensor types it knows; the
+# list is open for registration (torch/optim/optimizer.py: _foreach_supported_types).  Without this
+# an inner optimizer stepping our masters itself (no fused kernel for it) would silently take the
+# slower single-tensor loop, whose roundings differ from the foreach kernels the reference gets with
+# its plain fp32 masters.
+try:
+    from torch.optim.optimizer import _foreach_supported_types as _foreach_types
+    if _MasterParam not in _foreach_types:
+        _foreach_types.append(_MasterParam)
+except ImportError:          # older torch: no foreach selection by type
+    pass
+
+
 def _raw_grad(t):
     """``t.grad`` without triggering materialisation."""
     return _tensor_grad.__get__(t)
@@ -706,6 +719,17 @@ class FP16_Optimizer(object):
         self.overflow = state_dict['overflow']
         self.first_closure_call_this_step = state_dict['first_closure_call_this_step']
         self.optimizer.load_state_dict(state_dict['optimizer_state_dict'])
+        # A checkpoint loaded with map_location -> cuda brings Adam's step counters to the device, where
+        # torch reads each of them back every step (non-capturable mode) and our launch plan would
+        # decline: keep them where torch itself creates them, on the host.
+        if self._fused_kind() == "adam":
+            for group in self.optimizer.param_groups:
+                if group.get('capturable') or group.get('fused'):
+                    continue
+                for p in group['params']:
+                    st = self.optimizer.state.get(p)
+                    if st and isinstance(st.get('step'), torch.Tensor) and st['step'].is_cuda:
+                        st['step'] = st['step'].cpu()
         for current_group, saved_group in zip(self.fp32_from_fp16_groups, state_dict['fp32_from_fp16']):
             for current, saved in zip(current_group, saved_group):
                 current.data.copy_(saved.data)

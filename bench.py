@@ -648,6 +648,98 @@ def resnet50_training(dev, rank, world, steps=10, warmup=6, batch=64):
         del model, net, opt
         torch.cuda.empty_cache()
         return info
+    def reference_composition():
+        """What the reference runs on these GPUs today, written out with stock torch calls (never used
+        by our arm): per-bucket cat -> NCCL all_reduce -> /= world -> n x copy_ on a side stream from
+        gradient hooks (apex/parallel/distributed.py:11-23, :243-315; buckets by the rule of :248-261 for
+        reverse-order arrival), then per-tensor float(g.float().sum()) overflow test with a host sync
+        each (loss_scaler.py:84-110), per-tensor copy_ into fp32 master gradients and mul_(1/scale)
+        (fp16util.py:106-112, fp16_optimizer.py:236-241), torch.optim step, per-tensor copy_ back."""
+        torch.manual_seed(0)
+        net = network_to_half(torchvision.models.resnet50().to(dev))
+        params = [p for p in net.parameters() if p.requires_grad]
+        masters = [p.detach().clone().float().requires_grad_(True) if p.dtype == torch.float16 else p for p in params]
+        opt = torch.optim.SGD(masters, **SGD)
+        scale = 2.0**10
+        layout = reference_bucket_rule([p.numel() for p in params], [p.dtype for p in params], 10000000)
+        where = {i: b for b, members in enumerate(layout) for i in members}
+        side = torch.cuda.Stream()
+        st = {"next": 0, "ready": set(), "count": [0] * len(layout)}
+
+        def reduce_bucket(k):
+            side.wait_stream(torch.cuda.current_stream())
+            with torch.cuda.stream(side):
+                grads = [params[j].grad for j in layout[k]]
+                flat = torch.cat([g.reshape(-1) for g in grads])
+                dist.all_reduce(flat)
+                flat /= world
+                at = 0
+                for g in grads:
+                    g.copy_(flat[at:at + g.numel()].view_as(g))
+                    at += g.numel()
+
+        def hook_for(i):
+            def hook(_p):
+                b = where[i]
+                st["count"][b] += 1
+                if st["count"][b] == len(layout[b]):
+                    st["ready"].add(b)
+                    while st["next"] in st["ready"]:
+                        reduce_bucket(st["next"])
+                        st["next"] += 1
+            return hook
+        if world > 1:
+            for i, p in enumerate(params):
+                p.register_post_accumulate_grad_hook(hook_for(i))
+        g = torch.Generator(device=dev).manual_seed(77 + rank)
+        x = torch.randn(batch, 3, 224, 224, generator=g, device=dev)
+        y = torch.randint(0, 1000, (batch,), generator=g, device=dev)
+        crit = torch.nn.CrossEntropyLoss().to(dev)
+
+        def it():
+            loss = crit(net(x), y)
+            for p in params:                               # FP16_Optimizer.zero_grad (:187-211)
+                if p.grad is not None:
+                    p.grad.detach_()
+                    p.grad.zero_()
+            st["next"], st["ready"], st["count"] = 0, set(), [0] * len(layout)
+            (loss.float() * scale).backward()
+            torch.cuda.current_stream().wait_stream(side)
+            for p in params:                               # has_overflow: a host sync per tensor
+                s_ = float(p.grad.float().sum())
+                if s_ == float("inf") or s_ == -float("inf") or s_ != s_:
+                    return
+            for p, m in zip(params, masters):
+                if m is not p:
+                    if m.grad is None:
+                        m.grad = torch.empty_like(m)
+                    m.grad.copy_(p.grad)
+            for m in masters:
+                m.grad.mul_(1. / scale)
+            opt.step()
+            for p, m in zip(params, masters):
+                if m is not p:
+                    p.data.copy_(m.data)
+        for _ in range(warmup):
+            it()
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        for _ in range(steps):
+            it()
+        b.record()
+        torch.cuda.synchronize()
+        ms = a.elapsed_time(b) / steps
+        if world > 1:
+            t = torch.tensor([ms], device=dev, dtype=torch.float64)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            ms = float(t.item())
+        del net, opt, masters, params
+        torch.cuda.empty_cache()
+        return ms
+
     local = run(False)
     out = {"model": "torchvision resnet50, network_to_half (BatchNorm fp32), batch %d x 3 x 224 x 224 per GPU, "
                     "synthetic" % batch, "optimizer": "FP16_Optimizer(SGD momentum 0.9 wd 1e-4, dynamic loss scale)",
@@ -663,6 +755,13 @@ def resnet50_training(dev, rank, world, steps=10, warmup=6, batch=64):
     else:
         out["images_per_s"] = out["local_images_per_s"]
         out["skipped_steps"] = local["skipped_steps"]
+    ref_ms = reference_composition()
+    ours_ms = out.get("ddp_step_ms", out["local_step_ms"])
+    out["reference_composition_on_gpu"] = {
+        "step_ms": ref_ms, "images_per_s": world * batch / (ref_ms * 1e-3), "speedup_of_ours": ref_ms / ours_ms,
+        "what": "same model, batch and loop with the reference's composition of stock torch ops on these GPUs "
+                "(hook-driven per-bucket cat / NCCL all_reduce / div / copy_ on a side stream, per-tensor overflow "
+                "test with host syncs, copy_, mul_, torch.optim.SGD, copy_), static scale 2^10"}
     return out
 
 

@@ -64,6 +64,7 @@ def test_save_load_on_gpu_continues_bit_exactly(tmp_path, opt_name):
     assert float(opt_c.loss_scale) == float(opt_b.loss_scale) and opt_c.loss_scaler.cur_iter == opt_b.loss_scaler.cur_iter
     _run(opt_c, resumed, second)
 
+    assert opt_c.unfused_steps == 0                      # the resumed run stays on the fused kernels
     assert float(opt_c.loss_scale) == float(opt_a.loss_scale)
     assert opt_c.loss_scaler.cur_iter == opt_a.loss_scaler.cur_iter
     assert opt_c.loss_scaler.last_overflow_iter == opt_a.loss_scaler.last_overflow_iter
