@@ -19,6 +19,7 @@ from .. import _C
 from ..multi_tensor import TensorTable, CHUNK_STREAM, is_dense
 
 TENSOR_ALIGN_BYTES = 32
+SLICE_ALIGN_BYTES = 2048
 
 
 def bucket_layout(tensors, world):
@@ -29,7 +30,10 @@ def bucket_layout(tensors, world):
     for t in tensors:
         offsets.append(at)
         at += (t.numel() + step - 1) // step * step
-    unit = (16 // es) * max(world, 1)
+    # every rank's slice of the bucket starts on a SLICE_ALIGN_BYTES boundary: NVLink/NVSwitch requests
+    # of a warp (512 B) then never straddle 128 B lines (and the C ABI's rule, a whole number of
+    # 16 B vectors per rank, is implied)
+    unit = (SLICE_ALIGN_BYTES // es) * max(world, 1)
     unit = unit * step // _gcd(unit, step)
     total = (at + unit - 1) // unit * unit
     return offsets, max(total, unit)

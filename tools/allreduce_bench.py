@@ -74,4 +74,39 @@ for mb in sizes:
             report("ours %s ctas=%s (sum, x1/N, check, barriers)" % (mode, ctas or "default"),
                    timed(lambda: arena.allreduce(off, n, torch.float16, world, flag_off)), nbytes)
             assert int(flag.item()) == 0 and abs(float(view[0]) - 0.001) < 1e-4, (float(view[0]), int(flag.item()))
+
+# ---- the bench's situation: one round = the whole GPT-2-XL gradient set (3.1 GB) as K contiguous buckets,
+# launched back to back; optionally an HBM-bound kernel of the length of the fused Adam between rounds
+if os.environ.get("SPAN", "0") == "1":
+    del arena
+    torch.cuda.empty_cache()
+    total = symm.padded_numel(1557611200, 2, world * 16)
+    big = symm.Arena(total * 2 + (1 << 20), dev)
+    bflag, bflag_off = big.new_flag()
+    base = symm.HEADER_BYTES
+    big.buf[base:base + total * 2].view(torch.float16).fill_(0.001)
+    filler_a = torch.empty(1 << 30, dtype=torch.float32, device=dev)
+    filler_b = torch.empty(1 << 30, dtype=torch.float32, device=dev)
+    symm._force_p2p, symm._force_mc = False, False
+    for ctas in (0, 16):
+        symm._ctas = ctas
+        for k in (1, 3, 6, 11, 44, 145):
+            per = symm.padded_numel(total // k, 2, world * 16)
+            spans = []
+            at = 0
+            while at < total:
+                n = min(per, total - at)
+                spans.append((base + at * 2, n))
+                at += n
+
+            def round_(with_filler=False):
+                if with_filler:
+                    filler_b.copy_(filler_a)           # ~8.6 GB of HBM traffic, about 1.3 ms
+                for off, n in spans:
+                    big.allreduce(off, n, torch.float16, world, bflag_off)
+            report("3.1 GB as %d buckets ctas=%s" % (len(spans), ctas or "default"), timed(round_, reps=5), total * 2)
+            if k == 11:
+                ms = timed(lambda: round_(True), reps=5)
+                ms_f = timed(lambda: filler_b.copy_(filler_a), reps=5)
+                report("  same, an HBM copy before each round (copy alone %.3f ms)" % ms_f, ms - ms_f, total * 2)
 dist.destroy_process_group()
