@@ -54,7 +54,7 @@ class AdamArgs(ctypes.Structure):
 
 SYMM_MAX_WORLD = 16
 SYMM_MAX_CTAS = 256
-SYMM_CHANNELS = 2
+SYMM_CHANNELS = 4
 SYMM_SIGNAL_BYTES = SYMM_CHANNELS * SYMM_MAX_CTAS * SYMM_MAX_WORLD * 4
 
 

@@ -176,6 +176,14 @@ class _BucketPipeline(object):
     def __init__(self, gather_stream):
         self.gather_stream = gather_stream
         self.scatter_stream = torch.cuda.Stream()
+        # symmetric path: consecutive buckets rotate over a few collective streams (one signal
+        # channel each), so that the barriers / ramp-up of bucket b+1 overlap the drain of bucket
+        # b; the submitting stream only carries stray copy-ins and the events that release the
+        # kernels.  The choice depends on the bucket's position in the round only: same on every
+        # rank.  APEX_B200_SYMM_STREAMS=1: everything on the submitting stream.
+        n_comm = symm.comm_stream_count()
+        self.comm_streams = [torch.cuda.Stream() for _ in range(n_comm)] if n_comm > 1 else None
+        self._symm_count = 0
         self.slots = {}                # key -> (GradBucket, Arena or None, byte offset)
         self.arenas = []               # symmetric allocations of the current plan
         self._arena_flags = {}         # id(arena) -> (int32[1] view, byte offset)
@@ -193,6 +201,7 @@ class _BucketPipeline(object):
         self._round_id += 1
         self._token = None
         self._armed = True
+        self._symm_count = 0
 
     def _flag_of(self, arena):
         got = self._arena_flags.get(id(arena))
@@ -311,9 +320,26 @@ class _BucketPipeline(object):
         home.copy_in(bucket, strays)
         if arena is not None:
             word, word_off = self._flag_of(arena)
-            arena.allreduce(offset, home.padded, home.dtype, world, word_off)
-            if strays and owners is None:
-                home.copy_out(bucket, strays)
+            # Two kernels that wait for their peers may only be in flight together if all their CTAs
+            # fit on the GPU at once (else rank A could hold its SMs with bucket b while rank B holds
+            # its SMs with bucket b+1: a circular wait).  The multicast kernel is small (32 CTAs, 38
+            # registers); the peer-to-peer one fills the GPU (148 CTAs x 512 threads x ~120 registers)
+            # and therefore stays on one stream.
+            if self.comm_streams is None or not arena.use_multicast():
+                arena.allreduce(offset, home.padded, home.dtype, world, word_off, 0)
+                if strays and owners is None:
+                    home.copy_out(bucket, strays)
+            else:
+                channel = self._symm_count % len(self.comm_streams)
+                self._symm_count += 1
+                ready = torch.cuda.Event()
+                ready.record()                       # gradients final, strays copied in, word cleared
+                cs = self.comm_streams[channel]
+                with torch.cuda.stream(cs):
+                    cs.wait_event(ready)
+                    arena.allreduce(offset, home.padded, home.dtype, world, word_off, channel)
+                    if strays and owners is None:
+                        home.copy_out(bucket, strays)
         else:
             work = dist.all_reduce(home.flat, async_op=True)
             with torch.cuda.stream(self.scatter_stream):
@@ -335,6 +361,8 @@ class _BucketPipeline(object):
         usable by work enqueued on ``stream``."""
         stream.wait_stream(self.gather_stream)
         stream.wait_stream(self.scatter_stream)
+        for cs in self.comm_streams or ():
+            stream.wait_stream(cs)
         if len(self._used_arenas) > 1 or (self._used_arenas and
                                           self._flag_of(self._used_arenas[0])[0].data_ptr() != self.check_flag.data_ptr()):
             # buckets of several allocations raised several words: fold them into the round's

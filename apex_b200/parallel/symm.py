@@ -10,9 +10,9 @@ tests the result for inf/NaN and waits for its peers again -- where the referenc
 gradients (apex/fp16_utils/fp16_optimizer.py:213-221).
 
 Layout of one allocation (``Arena``):
-    [0, 32 KiB)        signal words of the in-kernel barriers  [channel][cta][rank] uint32
-    [48 KiB, +256 B)   overflow words (int32), one per user of the arena
-    [64 KiB, ...)      buckets, 256 B aligned
+    [0, 64 KiB)        signal words of the in-kernel barriers  [channel][cta][rank] uint32
+    [96 KiB, +256 B)   overflow words (int32), one per user of the arena
+    [128 KiB, ...)     buckets, 256 B aligned
 
 APEX_B200_SYMM=0 keeps NCCL; if symmetric memory cannot be set up the NCCL path is used with a warning.
 """
@@ -30,8 +30,8 @@ _force_mc = os.environ.get("APEX_B200_SYMM_P2P", "") == "0"
 _broken = False
 _single_host = None
 
-HEADER_BYTES = 64 << 10
-FLAG_BASE = 48 << 10
+HEADER_BYTES = 128 << 10
+FLAG_BASE = 96 << 10
 MAX_FLAGS = 64
 ALIGN = 256
 
@@ -66,6 +66,12 @@ def mark_broken(err):
     _broken = True
     import warnings
     warnings.warn("apex_b200: symmetric-memory allreduce unavailable (%s); using NCCL" % (err,))
+
+
+def comm_stream_count():
+    """How many collective streams / signal channels consecutive buckets rotate over
+    (APEX_B200_SYMM_STREAMS, default 4, at most the ABI's channel count); 1 = the submitting stream."""
+    return max(1, min(int(os.environ.get("APEX_B200_SYMM_STREAMS", "4")), _C.SYMM_CHANNELS))
 
 
 def _timeout_ns():

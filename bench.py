@@ -556,14 +556,30 @@ def side_configs(dev):
     return out
 
 
-def default_bucket_path(params, dev, world, rounds=5, warmup=2):
+def nvlink_roofline(s_bytes, ms, world):
+    """B200_PROFILING.md: bytes that must cross NVLink per direction per GPU / the measured 770 GB/s peer
+    copy rate.  Two-shot over the switch multicast: every GPU sends its copy of all slices up (S) and the
+    reduced slice it owns (S/n), and receives as much.  Two-shot with peer loads/stores: 2(n-1)/n * S."""
+    from apex_b200.parallel import symm as _symm
+    if not _symm.enabled():
+        return None
+    multicast = world > 2 and not _symm._force_p2p
+    per_dir = s_bytes * (1.0 + 1.0 / world) if multicast else s_bytes * 2.0 * (world - 1) / world
+    floor_ms = per_dir / 770e9 * 1e3
+    return {"bytes_per_direction": per_dir, "measured_peer_copy_gbs": 770.0, "floor_ms": floor_ms,
+            "achieved_gbs_per_direction": per_dir / (ms * 1e-3) / 1e9, "frac": floor_ms / ms,
+            "variant": "multicast" if multicast else "peer-to-peer"}
+
+
+def default_bucket_path(params, dev, world, rounds=5, warmup=2, message_size=10000000):
     """The bucket path of the headline's gradients at the reference's DEFAULT bucket size
-    (message_size = 10,000,000 elements = 20 MB of fp16, apex/parallel/distributed.py:124)."""
+    (message_size = 10,000,000 elements = 20 MB of fp16, apex/parallel/distributed.py:124), or at any
+    other ``message_size`` (BASELINE.json config 5: the sweep 1-256 MB, `bench.py --bucket-sweep`)."""
     import torch.distributed as dist
     from apex_b200.parallel.distributed import _BucketPipeline
     side = torch.cuda.Stream()
     pipeline = _BucketPipeline(side)
-    buckets = [[params[i] for i in b] for b in build_buckets(params, 10000000)]
+    buckets = [[params[i] for i in b] for b in build_buckets(params, message_size)]
     pipeline.plan([(k, [p.data for p in b]) for k, b in enumerate(buckets)])
     cur = torch.cuda.current_stream()
 
@@ -589,7 +605,8 @@ def default_bucket_path(params, dev, world, rounds=5, warmup=2):
     ms = float(t.item())
     nbytes = sum(p.numel() * p.element_size() for p in params)
     algbw = nbytes / (ms * 1e-3) / 1e9
-    return {"message_size": 10000000, "bucket_mb": 20.0, "buckets": len(buckets), "ms": ms, "algbw_gbs": algbw,
+    return {"message_size": message_size, "bucket_mb": message_size * 2 / (1 << 20), "buckets": len(buckets), "ms": ms,
+            "algbw_gbs": algbw,
             "busbw_gbs": algbw * 2 * (world - 1) / world, "frac_of_900": algbw * 2 * (world - 1) / world / 900.0}
 
 
@@ -798,6 +815,8 @@ def main():
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-gpu-reference", action="store_true")
+    ap.add_argument("--bucket-sweep", action="store_true",
+                    help="N > 1: only time the bucket path of the workload's gradients for bucket sizes 1..256 MB")
     ap.add_argument("--no-side-runs", action="store_true",
                     help="skip the short runs of configs 2-4, the default bucket size and ResNet-50 training")
     args = ap.parse_args()
@@ -850,6 +869,24 @@ def main():
     grads = [(torch.randn(s, generator=ggen, device=dev) * (1e-3 * 65536)).to(p.dtype) for s, p in zip(shapes, params)]
     for p, g in zip(params, grads):
         p.grad = g
+
+    if args.bucket_sweep:
+        if world < 2:
+            raise SystemExit("--bucket-sweep needs --gpus >= 2")
+        sweep = []
+        for mb in (1, 2, 4, 8, 16, 32, 64, 128, 256):
+            r = default_bucket_path(params, dev, world, rounds=3, warmup=2, message_size=mb * (1 << 20) // 2)
+            r["nvlink_roofline"] = nvlink_roofline(2 * n_params, r["ms"], world)
+            sweep.append(r)
+            if rank == 0:
+                sys.stderr.write("bucket %4d MB: %4d buckets %8.3f ms  busbw %6.1f GB/s\n"
+                                 % (mb, r["buckets"], r["ms"], r["busbw_gbs"]))
+        if rank == 0:
+            emit({"metric": "bucket_allreduce_path_ms", "n_gpus": world, "workload": args.workload, "bytes": 2 * n_params,
+                  "what": "whole bucket path (gradients living in the buckets: one kernel per bucket) per bucket size",
+                  "sweep": sweep})
+        dist.destroy_process_group()
+        return 0
 
     side = torch.cuda.Stream()
     pipeline = _BucketPipeline(side)
@@ -954,14 +991,41 @@ def main():
     # ---- end to end through the public API, gradients arriving from pinned HOST memory ----------
     e2e = None
     if not args.no_e2e:
-        host = [torch.empty(p.grad.shape, dtype=p.grad.dtype).pin_memory() for p in params]
-        for h, p in zip(host, params):
+        # The step's inputs arrive from pinned host memory in a FEW LARGE copies (one cudaMemcpyAsync per
+        # contiguous span), not one per tensor: at N > 1 the gradients already live in the flat buckets
+        # (one span per bucket); at N = 1 the user keeps them as views of one flat buffer, which is any
+        # caller's choice of layout (fp32-native gradients, if any, keep their own small tensors).
+        spans = []                                               # (device flat, pinned host flat)
+        loose = []
+        if world > 1:
+            for k in range(len(buckets)):
+                spans.append(pipeline.slots[k][0].flat)
+        else:
+            halves = [p for p in params if p.grad.dtype == torch.float16]
+            loose = [p for p in params if p.grad.dtype != torch.float16]
+            offs, at = [], 0
+            for p in halves:
+                offs.append(at)
+                at += (p.numel() + 15) // 16 * 16                # 32-byte aligned views
+            flat_grads = torch.zeros(at, dtype=torch.float16, device=dev)
+            for p, o in zip(halves, offs):
+                view = flat_grads[o:o + p.numel()].view(p.shape)
+                view.copy_(p.grad)
+                p.grad = view
+            spans.append(flat_grads)
+        host = [torch.empty(f.shape, dtype=f.dtype).pin_memory() for f in spans]
+        for h, f in zip(host, spans):
+            h.copy_(f)
+        loose_host = [torch.empty(p.grad.shape, dtype=p.grad.dtype).pin_memory() for p in loose]
+        for h, p in zip(loose_host, loose):
             h.copy_(p.grad)
-        h2d = sum(h.numel() * h.element_size() for h in host)
+        h2d = sum(h.numel() * h.element_size() for h in host + loose_host)
 
         def e2e_step():
-            for p, h in zip(params, host):
-                p.grad.copy_(h, non_blocking=True)            # this step's inputs: host -> device
+            for f, h in zip(spans, host):
+                f.copy_(h, non_blocking=True)                     # this step's inputs: host -> device
+            for p, h in zip(loose, loose_host):
+                p.grad.copy_(h, non_blocking=True)
             step()
             return opt.overflow                               # the step's result: device -> host (4 bytes)
         for _ in range(2):
@@ -983,8 +1047,10 @@ def main():
             e2e_ms = float(t.item())
         e2e = {"value": world * n_params / (e2e_ms * 1e-3), "unit": "params/s", "h2d_bytes_per_step": h2d,
                "d2h_bytes_per_step": 4, "ms_per_step": e2e_ms, "steps": n_e2e,
-               "api": "param.grad.copy_(pinned host) ; FP16_Optimizer.update_master_grads() ; .step() ; .overflow"}
-        del host
+               "h2d_copies_per_step": len(host) + len(loose_host),
+               "api": "gradients.copy_(pinned host), one copy per contiguous span ; "
+                      "FP16_Optimizer.update_master_grads() ; .step() ; .overflow"}
+        del host, spans
 
     parity = None
     if world > 1:
@@ -1065,6 +1131,7 @@ def main():
                                               "(NVSwitch multimem beyond 2 ranks, peer-to-peer at 2), x 1/N, inf/NaN "
                                               "check, barrier" if _symm.enabled() else "NCCL",
                                  "kernel": kernel,
+                                 "nvlink_roofline": nvlink_roofline(s_bytes, comm_ms, world),
                                  "busbw_gbs": algbw * 2 * (world - 1) / world, "nvlink_peak_gbs_per_dir": 900.0,
                                  "frac_of_900": algbw * 2 * (world - 1) / world / 900.0,
                                  "includes": "whole bucket path from the end of backward to averaged, checked gradients. "

@@ -258,7 +258,7 @@ int apex_b200_scale_flat(void* flat, int64_t numel, int dtype, double divisor,
  * the start, never reset) and, optionally, 4-byte overflow words. */
 #define APEX_B200_SYMM_MAX_WORLD 16
 #define APEX_B200_SYMM_MAX_CTAS 256
-#define APEX_B200_SYMM_CHANNELS 2
+#define APEX_B200_SYMM_CHANNELS 4
 #define APEX_B200_SYMM_SIGNAL_BYTES (APEX_B200_SYMM_CHANNELS * APEX_B200_SYMM_MAX_CTAS * APEX_B200_SYMM_MAX_WORLD * 4)
 
 typedef struct apex_b200_symm_domain {
