@@ -504,6 +504,12 @@ def test_clip_factor_folded_into_fused_step_and_materialisation(norm_value, max_
         assert np.array_equal(bits(d), c_oracle.f16_to_f32_scaled(bits(s), inv, True, coef))
         ref = s.float().mul_(inv).mul_(torch.tensor(coef, device=dev()))       # unscale, then clip_grad_norm_'s mul_
         assert torch.equal(d, ref)
+    # header contract: apply_scale == 0 means exact widening, also when a clip norm is given and the
+    # caller passes some inv_scale != 1 along (inv_scale leaked into this case)
+    dst0 = [torch.zeros(g.numel(), device=dev()) for g in src]
+    _C.mt_grads_to_master(table([src, dst0], None, 8192), 0, 1, inv, False, None, (norm, max_norm))
+    for s, d in zip(src, dst0):
+        assert torch.equal(d, s.float().mul_(torch.tensor(coef, device=dev())))
     # SGD with momentum
     bufs = [torch.zeros_like(m) for m in masters]
     o_p = [bits(m).copy() for m in masters]
