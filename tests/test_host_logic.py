@@ -747,3 +747,36 @@ def test_storage_swapped_under_an_unchanged_identity_is_noticed(cpu_backend):
         assert torch.equal(p.data, r.data)
     for m, rm in zip(opt.fp32_from_fp16_groups[0], ref.masters):
         assert torch.equal(m.data, rm.data)
+
+
+def test_bucket_layout_alignment_and_views():
+    """parallel/buckets.py: members on 32 B boundaries, every rank's slice on a 2 KiB boundary, views alias
+    the flat buffer with the member's shape AND strides (channels-last too) and own version counters."""
+    from apex_b200.parallel.buckets import GradBucket, bucket_layout, SLICE_ALIGN_BYTES
+    for world in (1, 2, 3, 8):
+        for dtype in (torch.float16, torch.float32):
+            like = [torch.zeros(n, dtype=dtype) for n in (5, 4099, 64, 1000, 1)]
+            offs, padded = bucket_layout(like, world)
+            es = like[0].element_size()
+            assert all((o * es) % 32 == 0 for o in offs)
+            assert all(b - a >= t.numel() for a, b, t in zip(offs, offs[1:] + [padded], like))
+            assert (padded * es) % (SLICE_ALIGN_BYTES * world) == 0
+            assert (padded // world * es) % 16 == 0                       # the C ABI's own rule
+    cl = torch.zeros(4, 3, 5, 5).to(memory_format=torch.channels_last)
+    like = [torch.zeros(7, 9), cl, torch.zeros(11)]
+    home = GradBucket(like, 2)
+    assert home.flat.numel() == home.padded and float(home.flat.abs().sum()) == 0.0
+    for v, t in zip(home.views, like):
+        assert v.shape == t.shape and v.stride() == t.stride()
+        lo = home.flat.data_ptr()
+        assert lo <= v.data_ptr() < lo + home.flat.numel() * 4
+    home.views[0].add_(1.0)
+    assert home.views[0]._version == 1 and home.views[1]._version == 0     # not shared
+    assert float(home.flat.sum()) == 63.0                                   # ... but the memory is
+    assert home.fits(like) and not home.fits(like[:2]) and not home.fits([like[0], like[1].contiguous(), like[2]])
+    assert home.strays(list(home.views)) == []
+    assert home.strays([home.views[0], torch.zeros_like(cl), home.views[2]]) == [1]
+    with pytest.raises(TypeError):
+        GradBucket([torch.zeros(3), torch.zeros(3).half()], 2)
+    with pytest.raises(RuntimeError, match="dense"):
+        GradBucket([torch.zeros(4, 4)[:, :2]], 2)
