@@ -320,24 +320,20 @@ class _BucketPipeline(object):
         home.copy_in(bucket, strays)
         if arena is not None:
             word, word_off = self._flag_of(arena)
-            # Two kernels that wait for their peers may only be in flight together if all their CTAs
-            # fit on the GPU at once (else rank A could hold its SMs with bucket b while rank B holds
-            # its SMs with bucket b+1: a circular wait).  The multicast kernel is small (32 CTAs, 38
-            # registers); the peer-to-peer one fills the GPU (148 CTAs x 512 threads x ~120 registers)
-            # and therefore stays on one stream.
-            if self.comm_streams is None or not arena.use_multicast():
-                arena.allreduce(offset, home.padded, home.dtype, world, word_off, 0)
+            streams, ctas = arena.rotation() if self.comm_streams is not None else (1, None)
+            if streams == 1:
+                arena.allreduce(offset, home.padded, home.dtype, world, word_off, 0, ctas=ctas)
                 if strays and owners is None:
                     home.copy_out(bucket, strays)
             else:
-                channel = self._symm_count % len(self.comm_streams)
+                channel = self._symm_count % streams
                 self._symm_count += 1
                 ready = torch.cuda.Event()
                 ready.record()                       # gradients final, strays copied in, word cleared
                 cs = self.comm_streams[channel]
                 with torch.cuda.stream(cs):
                     cs.wait_event(ready)
-                    arena.allreduce(offset, home.padded, home.dtype, world, word_off, channel)
+                    arena.allreduce(offset, home.padded, home.dtype, world, word_off, channel, ctas=ctas)
                     if strays and owners is None:
                         home.copy_out(bucket, strays)
         else:

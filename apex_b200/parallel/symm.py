@@ -133,12 +133,27 @@ class Arena(object):
     def use_multicast(self):
         return self.has_multicast and not _force_p2p and (_force_mc or self.world > 2)
 
-    def allreduce(self, offset, numel, dtype, divisor, flag_offset, channel=0, apply_mul=True):
+    def rotation(self):
+        """(streams, CTAs per kernel) for buckets in flight together.  Kernels that wait for their
+        peers may only overlap on a GPU if ALL their CTAs are resident at once (else rank A could fill
+        its SMs with bucket b while rank B fills its SMs with bucket b+1: a circular wait).  The
+        multicast kernel is small (32 CTAs x 512 threads x 38 registers: four of them fit many times
+        over); the peer-to-peer kernel needs a whole SM per CTA (512 threads x ~120 registers), so two
+        of them share the 148 SMs with 74 CTAs each."""
+        n = comm_stream_count()
+        if self.use_multicast():
+            return n, (_ctas if _ctas > 0 else 32)
+        if n >= 2 and _ctas <= 0:
+            return 2, 74
+        return 1, (_ctas if _ctas > 0 else 148)
+
+    def allreduce(self, offset, numel, dtype, divisor, flag_offset, channel=0, apply_mul=True, ctas=None):
         """This rank's kernel of the averaging of [offset, offset + numel * itemsize) on the current
         stream.  Every rank must issue the same sequence of calls per channel."""
         self.seq[channel] += 1
         mc = self.use_multicast()
-        ctas = _ctas if _ctas > 0 else (32 if mc else 148)
+        if ctas is None:
+            ctas = _ctas if _ctas > 0 else (32 if mc else 148)
         _C.symm_allreduce(self.domain, offset, numel, dtype, divisor, apply_mul,
                           -1 if flag_offset is None else flag_offset, channel, self.seq[channel], mc, ctas)
 
