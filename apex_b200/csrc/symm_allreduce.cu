@@ -70,14 +70,15 @@ __device__ __forceinline__ unsigned long long global_ns() {
 }
 
 // Thread t < world tells peer t "CTA blockIdx.x of rank `rank` reached `epoch`" and waits for the
-// same word from peer t.  The __syncthreads + system fence before the release make every earlier
-// store of the whole CTA (data and flag) visible to a peer that has seen the word.
+// same word from peer t.  The release is cumulative: everything the signalling thread has observed
+// through the CTA barrier -- every earlier store of the whole CTA, data and flag -- is visible to a
+// peer that has acquired the word (SASS: MEMBAR.ALL.SYS in front of the signal store; an extra
+// __threadfence_system() here only added a second, sequentially consistent fence per barrier).
 __device__ __forceinline__ void symm_barrier(const SymmArgs& a, uint32_t epoch) {
     __syncthreads();
     if (threadIdx.x < a.world) {
         const int peer = threadIdx.x;
         const size_t slot = size_t(blockIdx.x) * kMaxPeers;
-        __threadfence_system();
         st_release_sys(a.sig[peer] + slot + a.rank, epoch);
         const uint32_t* mine = a.sig[a.rank] + slot + peer;
         unsigned long long t0 = 0;
