@@ -1109,7 +1109,11 @@ def main():
             "roofline": roofline, "cpu_baseline": cpu, "reference_composition_on_gpu": gpu_ref, "e2e": e2e,
             "gpu_launches": launches, "clocks": clocks, "parity": parity, "side_runs": side_runs,
             "breakdown_ms": {"check_overflow": check_ms, "fused_update": fused_ms, "bucket_allreduce_path": comm_ms,
-                             "host_python_per_step": host_ms_per_step},
+                             # what the step spends outside these three (launch gaps, event records)
+                             "gaps": ms_per_step - check_ms - fused_ms - (comm_ms or 0.0),
+                             # wall time inside step() on the host: python + the wait for the overflow word
+                             # (which arrives with the check / the last bucket), NOT pure python time
+                             "host_time_in_step_incl_wait_for_flag": host_ms_per_step},
             "hbm_gbs_step": (bpp + 2) * n_params / (ms_per_step * 1e-3) / 1e9 if world == 1 else None,
         }
         if comm_ms:
