@@ -276,6 +276,28 @@ def _worker(rank, world, port, out_dir):
         ok[mode + "_in_symmetric_memory"] = bool(pipe.arenas)
     symm.enable(True)
     symm._force_p2p = symm._force_mc = False
+    # buckets that end up in DIFFERENT symmetric allocations (homes created one by one, the second
+    # does not fit the first arena): each arena has its own overflow word, join() folds them into
+    # the round's word
+    pipe = _BucketPipeline(torch.cuda.current_stream())
+    pipe.MIN_ARENA = 1 << 20
+    first = [torch.ones(300000, device="cuda").half()]
+    second = [torch.ones(1500000, device="cuda").half()]
+    if rank == 0:
+        second[0][777] = float("inf")
+    pipe.begin_round()
+    pipe.submit(0, first)
+    pipe.submit(1, second)
+    pipe.join(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    ok["two_arenas"] = len(pipe.arenas) == 2 and int(pipe.check_flag.item()) != 0 and bool((first[0] == 1).all()) \
+        and bool(torch.isinf(second[0][777]))
+    pipe.begin_round()
+    pipe.submit(0, [torch.ones(300000, device="cuda").half()])
+    pipe.submit(1, [torch.ones(1500000, device="cuda").half()])
+    pipe.join(torch.cuda.current_stream())
+    torch.cuda.synchronize()
+    ok["two_arenas"] &= int(pipe.check_flag.item()) == 0
     torch.save(ok, os.path.join(out_dir, "rank%d.pt" % rank))
     dist.barrier()
     dist.destroy_process_group()
@@ -299,7 +321,7 @@ def test_two_ranks_nccl(tmp_path):
                     "reducer_list", "reducer_broadcast", "reducer_module",
                     "symm_auto", "symm_p2p", "nccl_fallback",
                     "symm_auto_overflow", "symm_p2p_overflow", "nccl_fallback_overflow",
-                    "symm_auto_in_symmetric_memory", "symm_p2p_in_symmetric_memory"):
+                    "symm_auto_in_symmetric_memory", "symm_p2p_in_symmetric_memory", "two_arenas"):
             assert res[key] is True, (key, res)
         assert res["nccl_fallback_in_symmetric_memory"] is False
         print("world", WORLD, "rank", r, "| multicast used:", res["symm_auto_multicast"],
