@@ -154,6 +154,11 @@ def verified_flag(grads):
     return token.flag
 
 
+# what setting up symmetric memory can raise on a box or torch build that does not have it (the module
+# is a private torch API: missing, renamed or unsupported are all "use NCCL")
+_SYMM_SETUP_ERRORS = (RuntimeError, ImportError, AttributeError, NotImplementedError)
+
+
 class _BucketPipeline(object):
     """Averages gradient buckets in their persistent flat homes (parallel/buckets.py).
 
@@ -273,7 +278,7 @@ class _BucketPipeline(object):
             try:
                 storage, arena, off = self._symm_home(like, world)
                 return (GradBucket(like, world, storage), arena, off)
-            except RuntimeError as err:           # every rank fails alike: allocation + rendezvous are collective
+            except _SYMM_SETUP_ERRORS as err:     # every rank fails alike: allocation + rendezvous are collective
                 if "bucket tensors must be dense" in str(err):
                     raise
                 symm.mark_broken(err)
@@ -290,7 +295,7 @@ class _BucketPipeline(object):
                         for like in want) + symm.ALIGN
             try:
                 self.arenas.append(symm.Arena(total, want[0][0].device))
-            except RuntimeError as err:
+            except _SYMM_SETUP_ERRORS as err:
                 symm.mark_broken(err)
         for key, like in buckets:
             if like:

@@ -157,6 +157,80 @@ def test_gradients_move_into_their_buckets(gloo_single):
     assert all(torch.equal(p.grad, q.grad) for p, q in zip(net.parameters(), ref.parameters()))
 
 
+def test_symmetric_path_host_logic_with_a_fake_arena(gloo_single, monkeypatch):
+    """The host side of the symmetric-memory bucket path without NVLink: homes carved out of ONE
+    allocation by plan(), gradients re-homed, one allreduce call per bucket with per-channel sequence
+    numbers that only depend on the bucket's position in the round, the round's overflow word living in
+    the allocation.  (The kernel itself is covered by the multi-GPU tests.)"""
+    from apex_b200.parallel import symm
+    from apex_b200.parallel import distributed as D
+    calls = []
+
+    class FakeArena(object):
+        def __init__(self, payload, device):
+            self.nbytes = symm.HEADER_BYTES + int(payload)
+            self.buf = torch.zeros(self.nbytes, dtype=torch.uint8)
+            self.used = symm.HEADER_BYTES
+            self.seq = [0, 0, 0, 0]
+            self.flags = self.buf[symm.FLAG_BASE:symm.FLAG_BASE + 256].view(torch.int32)
+            self.n_flags = 0
+
+        def take(self, nbytes):
+            start = (self.used + 255) // 256 * 256
+            if start + nbytes > self.nbytes:
+                return None
+            self.used = start + nbytes
+            return start
+
+        def new_flag(self):
+            self.n_flags += 1
+            return self.flags[self.n_flags - 1:self.n_flags], symm.FLAG_BASE + 4 * (self.n_flags - 1)
+
+        def use_multicast(self):
+            return True
+
+        def rotation(self):
+            return 4, 32
+
+        def allreduce(self, offset, numel, dtype, divisor, flag_offset, channel=0, apply_mul=True, ctas=None):
+            self.seq[channel] += 1
+            calls.append((offset, numel, channel, self.seq[channel], flag_offset, ctas))
+            flat = self.buf[offset:offset + numel * dtype.itemsize].view(dtype)
+            if not torch.isfinite(flat.float()).all():                    # world 1: average = identity
+                self.buf[flag_offset:flag_offset + 4].view(torch.int32)[0] = 0x7fffffff
+    monkeypatch.setattr(symm, "enabled", lambda: True)
+    monkeypatch.setattr(symm, "Arena", FakeArena)
+    monkeypatch.setattr(D._BucketPipeline, "_wants_symm",
+                        staticmethod(lambda like: like[0].dtype in (torch.float16, torch.float32)))
+    pipe = D._BucketPipeline(gloo_single._Stream())
+    params = [torch.nn.Parameter(torch.zeros(n).half()) for n in (40, 7, 3000, 64, 5)]
+    buckets = [params[:2], params[2:4], params[4:]]
+    pipe.plan([(k, [p.data for p in b]) for k, b in enumerate(buckets)])
+    assert len(pipe.arenas) == 1                                          # one allocation for all buckets
+    offsets = [pipe.slots[k][2] for k in range(3)]
+    assert offsets == sorted(offsets) and offsets[0] >= symm.HEADER_BYTES and all(o % 256 == 0 for o in offsets)
+    for rnd in range(3):
+        for p in params:
+            if rnd != 1:                                                  # round 1: gradients kept (in place)
+                p.grad = torch.full_like(p, float(rnd + 1))
+        if rnd == 2:
+            params[2].grad[5] = float("nan")
+        del calls[:], gloo_single.calls[:]
+        pipe.begin_round()
+        for k, b in enumerate(buckets):
+            pipe.submit(k, [p.grad for p in b], verify=True, owners=b)
+        pipe.join(gloo_single._Stream())
+        assert [c[2] for c in calls] == [0, 1, 2]                         # channel = position in the round
+        assert [c[3] for c in calls] == [rnd + 1] * 3                     # one more per channel and round
+        assert [c[0] for c in calls] == offsets and all(c[5] == 32 for c in calls)
+        assert gloo_single.calls.count("copy") == (0 if rnd == 1 else 3)  # strays only
+        for k, b in enumerate(buckets):
+            assert all(p.grad is v for p, v in zip(b, pipe.slots[k][0].views))
+        assert int(pipe.check_flag[0] != 0) == int(rnd == 2)
+        assert pipe.check_flag.data_ptr() == pipe.arenas[0].flags.data_ptr()
+        assert D.verified_flag([p.grad for p in params]) is pipe.check_flag
+
+
 # ---- world size 2 -------------------------------------------------------------------------------
 
 def _install_double():
