@@ -8,13 +8,19 @@ buckets reduced strictly in index order on a side stream while backward keeps
 running; sum across ranks, then divide by the world size in the bucket's own
 dtype; the same three sanity errors.  The code is organised differently:
 
-* ``_BucketLayout`` -- the learned structure (what rank 0 dictates).
-* ``_BucketRound``  -- per-backward progress (which slots are filled, what may go).
-* ``_FlatSlot``     -- a persistent coalesced buffer + device tensor table per
-  bucket, so that the data path of one bucket is
-      1 gather launch -> NCCL collective -> 1 (x 1/world, scatter, inf/NaN check) launch
+* ``_BucketLayout``   -- the learned structure (what rank 0 dictates).
+* ``_BucketRound``    -- per-backward progress (which slots are filled, what may go).
+* ``_BucketPipeline`` -- the data path.  Every bucket has a persistent flat home
+  (parallel/buckets.py) that the gradients LIVE in: ``param.grad`` is a view of it
+  after the first overlapped backward, so a bucket is averaged in place by ONE launch
+  (parallel/symm.py + csrc/symm_allreduce.cu: barrier, sum across ranks, x 1/world,
+  inf/NaN check, barrier) -- or NCCL ``all_reduce`` + one in-place scale launch --
   instead of the reference's alloc + cat + allreduce + divide + n copy_ launches
-  (distributed.py:11-23).  A bucket of a single tensor is reduced in place.
+  (distributed.py:11-23).
+* ``_FlatSlot``       -- coalesced staging buffer + table for one-off flat calls on
+  arbitrary tensor lists (``flat_dist_call``: initial broadcast, the iteration that
+  learns the structure, ``Reducer``): 1 gather launch -> collective -> 1 (x 1/world,
+  scatter, inf/NaN check) launch.
 """
 import copy
 from collections import OrderedDict

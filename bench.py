@@ -12,8 +12,12 @@ end of backward and the next forward (apex/fp16_utils/fp16_optimizer.py:486-497,
 inf/NaN check of every gradient feeding DynamicLossScaler, unscale into fp32, Adam update of the
 fp32 masters, copy back to the fp16 parameters -- driven through apex_b200.fp16_utils.FP16_Optimizer.
 With N > 1 each rank first averages its gradients with the other ranks bucket by bucket
-(apex/parallel/distributed.py:11-23: gather -> NCCL all_reduce -> x 1/N + scatter) on a side
-stream, exactly the calls DistributedDataParallel makes per bucket.
+(apex/parallel/distributed.py:11-23: flatten, all_reduce, /= world, copy back -- here: the gradients
+live in the buckets and one kernel per bucket does barrier, sum, x 1/N, inf/NaN check, barrier) on
+side streams, exactly the calls DistributedDataParallel makes per bucket; afterwards, outside the
+timed region, the averaged gradients are checked against the reference composition (`parity`).
+Short side runs (BASELINE.json configs 2, 3, 4, the static-scale step, the reference's default
+bucket size, ResNet-50 training through DistributedDataParallel) follow the headline.
 
 `value` counts parameter elements updated per second over all ranks (weak scaling: every rank
 owns a full replica and its own gradients).
