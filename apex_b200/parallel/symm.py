@@ -137,12 +137,14 @@ class Arena(object):
         """(streams, CTAs per kernel) for buckets in flight together.  Kernels that wait for their
         peers may only overlap on a GPU if ALL their CTAs are resident at once (else rank A could fill
         its SMs with bucket b while rank B fills its SMs with bucket b+1: a circular wait).  The
-        multicast kernel is small (32 CTAs x 512 threads x 38 registers: four of them fit many times
-        over); the peer-to-peer kernel needs a whole SM per CTA (512 threads x ~120 registers), so two
+        multicast kernel is small (16-32 CTAs x 512 threads x 38 registers: four of them fit many
+        times over); the peer-to-peer kernel needs a whole SM per CTA (512 threads x ~120 registers), so two
         of them share the 148 SMs with 74 CTAs each."""
         n = comm_stream_count()
         if self.use_multicast():
-            return n, (_ctas if _ctas > 0 else 32)
+            # measured on 8 GPUs with 4 streams (3.1 GB): 16 CTAs per kernel 6.49 ms at 256 MB buckets
+            # and 7.06 ms at 20 MB; 24: 6.53 / 7.33; 32: 6.58 / 7.63
+            return n, (_ctas if _ctas > 0 else (16 if n >= 4 else 32))
         if n >= 2 and _ctas <= 0:
             return 2, 74
         return 1, (_ctas if _ctas > 0 else 148)
