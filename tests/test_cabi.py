@@ -240,3 +240,38 @@ def test_symm_allreduce_validates_before_any_cuda_call():
     assert "#define APEX_B200_SYMM_MAX_WORLD %d" % _C.SYMM_MAX_WORLD in header
     assert "#define APEX_B200_SYMM_MAX_CTAS %d" % _C.SYMM_MAX_CTAS in header
     assert "#define APEX_B200_SYMM_CHANNELS %d" % _C.SYMM_CHANNELS in header
+
+
+def test_struct_layouts_match_the_header(tmp_path):
+    """The ctypes mirrors in apex_b200/_C.py against what a C compiler makes of include/apex_b200.h."""
+    import ctypes
+    src = os.path.join(str(tmp_path), "layout.c")
+    exe = os.path.join(str(tmp_path), "layout")
+    fields = {
+        "apex_b200_mt_table": ["d_table", "n_tensors", "n_lists", "chunk_elems", "total_chunks"],
+        "apex_b200_sgd_args": ["lr", "momentum", "dampening", "weight_decay", "nesterov", "apply_scale", "inv_scale",
+                               "clip_norm", "clip_max_norm"],
+        "apex_b200_adam_args": ["lr", "beta1", "beta2", "eps", "weight_decay", "step_size", "bias_correction2_sqrt",
+                                "decoupled_weight_decay", "apply_scale", "inv_scale", "clip_norm", "clip_max_norm"],
+        "apex_b200_symm_domain": ["rank", "world", "peer_base", "multicast_base", "signal_offset", "timeout_ns"],
+    }
+    mirrors = {"apex_b200_mt_table": _C.MtTableStruct, "apex_b200_sgd_args": _C.SgdArgs,
+               "apex_b200_adam_args": _C.AdamArgs, "apex_b200_symm_domain": _C.SymmDomain}
+    lines = ['#include <stdio.h>', '#include <stddef.h>', '#include "apex_b200.h"', 'int main(void) {']
+    for name, fs in fields.items():
+        lines.append('printf("%s %%zu", sizeof(%s));' % (name, name))
+        for f in fs:
+            lines.append('printf(" %%zu", offsetof(%s, %s));' % (name, f))
+        lines.append('printf("\\n");')
+    lines += ['printf("signal_bytes %d\\n", APEX_B200_SYMM_SIGNAL_BYTES);', 'return 0; }']
+    with open(src, "w") as f:
+        f.write("\n".join(lines))
+    subprocess.check_call(["gcc", "-std=c99", "-I", os.path.join(ROOT, "include"), src, "-o", exe])   # plain C: the header is C
+    out = subprocess.check_output([exe]).decode().splitlines()
+    for line in out[:-1]:
+        parts = line.split()
+        mirror = mirrors[parts[0]]
+        assert ctypes.sizeof(mirror) == int(parts[1]), parts[0]
+        assert [getattr(mirror, f).offset for f, _ in mirror._fields_] == [int(x) for x in parts[2:]], parts[0]
+        assert [f for f, _ in mirror._fields_] == fields[parts[0]]
+    assert int(out[-1].split()[1]) == _C.SYMM_SIGNAL_BYTES
