@@ -511,7 +511,7 @@ class FP16_Optimizer(object):
             self.overflow = False
             return
         self._ensure_device(grads[0])
-        # Multi-GPU: DistributedDataParallel's scatter pass has already looked at every averaged
+        # Multi-GPU: DistributedDataParallel's allreduce kernel has already looked at every averaged
         # value it wrote; if that covers all of our gradients and nothing touched them since, its
         # flag word IS the answer and no extra pass over the gradients is needed.
         from ..parallel.distributed import verified_flag

@@ -122,7 +122,7 @@ def apply_flat_dist_call(bucket, call, extra_args=None, _slot=None, _flag=None):
 
 
 class _Verified(object):
-    """What a gradient tensor carries after its bucket went through the scatter-with-check pass:
+    """What a gradient tensor carries after its bucket went through the averaging-with-check kernel:
     which device word would have been raised had the averaged values held an inf/NaN, in which
     round, and the tensor's version counter at that moment (any later in-place torch op on the
     gradient changes the counter and voids the verification)."""
@@ -693,7 +693,7 @@ class DistributedDataParallel(Module):
         """``param``'s gradient is final: file it, and reduce whatever became eligible on
         the side stream (reference: :279-315)."""
         bucket_idx, bucket_loc = self._where[id(param)]
-        # the gradient tensor itself (not a `.data` alias): the scatter pass tags the very object the
+        # the gradient tensor itself (not a `.data` alias): the pipeline tags the very object the
         # optimizer will later find in param.grad
         eligible = self._round.put(bucket_idx, bucket_loc, param.grad)
         if not eligible:
