@@ -327,8 +327,26 @@ def _worker(rank, world, port, out_dir):
             want = local * torch.tensor(0.5)
             same &= torch.equal(p.grad, want)
     ok["ddp_average"] = bool(same)
-    ok["ddp_layout"] = (ddp.num_buckets, list(ddp.bucket_sizes))
     ok["ddp_calls"] = sorted(set(fb.calls))
+    # gradients kept across iterations (zeroed in place): they live in the buckets, autograd accumulates
+    # into the views and the averaging runs in place -- no copy in, no copy out
+    del fb.calls[:]
+    inplace = True
+    for it in range(3):
+        g = torch.Generator().manual_seed(900 * it + rank)
+        xb = torch.randn(7, 6, generator=g)
+        net.zero_grad(set_to_none=False)
+        ref.zero_grad()
+        ddp(xb).pow(2).sum().backward()
+        ref(xb).pow(2).sum().backward()
+        for p, q in zip(net.parameters(), ref.parameters()):
+            local = q.grad.clone()
+            dist.all_reduce(local)
+            inplace &= torch.equal(p.grad, local * torch.tensor(0.5))
+    inplace &= all(p.grad is v for b, ps in enumerate(ddp._bucket_params)
+                   for p, v in zip(ps, ddp._pipeline.slots[b][0].views))
+    ok["ddp_in_place"] = bool(inplace) and "copy" not in fb.calls and "flatten" not in fb.calls
+    ok["ddp_layout"] = (ddp.num_buckets, list(ddp.bucket_sizes))
 
     # Reducer on a list of tensors and on a module
     t = [torch.full((3,), float(rank)), [torch.full((2,), 2.0 * rank).half()]]
@@ -352,9 +370,9 @@ def test_world_size_two(tmp_path):
     results = [torch.load(os.path.join(str(tmp_path), "rank%d.pt" % r), weights_only=False) for r in range(2)]
     for r in results:
         for key in ("flat_half", "flat_float", "fp16_sum_overflow_stays_inf", "race_known_answer", "race_buckets",
-                    "broadcast_from_rank0", "ddp_average", "reducer_list", "reducer_module"):
+                    "broadcast_from_rank0", "ddp_average", "ddp_in_place", "reducer_list", "reducer_module"):
             assert r[key] is True, (key, r)
-        assert {"flatten", "scale_unflatten", "scale_flat"} <= set(r["ddp_calls"])
+        assert {"flatten", "scale_unflatten", "scale_flat", "copy"} <= set(r["ddp_calls"])
     # rank 0 dictates the structure: identical on both ranks
     assert results[0]["ddp_layout"] == results[1]["ddp_layout"] == (3, [3, 1, 2])
 
